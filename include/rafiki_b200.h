@@ -1,0 +1,134 @@
+/*
+ * rafiki_b200 -- C ABI of the B200-native Rafiki serving hot path.
+ *
+ * The reference (vivansxu/rafiki) is pure Python and has no FFI of its own: its hot
+ * path is a Python plugin API (rafiki/model/model.py:20-127) whose arithmetic runs
+ * inside tensorflow==1.12.0 and NumPy.  This header is therefore the *new* boundary
+ * the Python drop-ins (rafiki_b200/model, rafiki_b200/predictor, rafiki_b200/worker)
+ * bind with ctypes; each entry point names the reference code it replaces.
+ *
+ * Conventions
+ *   - extern "C", plain pointers and sizes, no C++/torch types.
+ *   - Every call returns 0 on success, else an RFK_ERR_* code; rfk_last_error() then
+ *     holds a thread-local message.  Nothing throws.
+ *   - Data buffers are caller-owned DEVICE memory unless a parameter says HOST.
+ *   - `stream` is a cudaStream_t passed as void*; work is enqueued on it and the call
+ *     returns without synchronising, unless stated.
+ *   - sm_100a only.  There is no CPU fallback: without a B200 every compute entry
+ *     point fails with RFK_ERR_CUDA / RFK_ERR_UNSUPPORTED.
+ */
+#ifndef RAFIKI_B200_H
+#define RAFIKI_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RFK_VERSION 100
+
+#define RFK_OK 0
+#define RFK_ERR_INVALID 1     /* bad argument */
+#define RFK_ERR_CUDA 2        /* CUDA runtime/driver error */
+#define RFK_ERR_UNSUPPORTED 3 /* shape or device outside what the kernels cover */
+#define RFK_ERR_COMM 4        /* NCCL / peer-memory error */
+
+#define RFK_F32 0  /* fp32 CUDA-core arithmetic (parity path, <= 1e-5 of the oracle) */
+#define RFK_BF16 1 /* bf16 operands on tcgen05 tensor cores, fp32 accumulate */
+
+#define RFK_MAX_TRIALS 32  /* most trials one ensemble call accepts */
+#define RFK_MAX_CLASSES 16 /* most classes the fused kernels accept */
+
+typedef struct rfk_mlp rfk_mlp_t; /* one trial: packed TfFeedForward weights on one GPU */
+
+int rfk_version(void);
+const char* rfk_last_error(void);
+
+/* 0 when `device` is a compute-capability 10.x GPU this library can run on. */
+int rfk_device_check(int device);
+
+/*
+ * Kernel 1 -- query decode / normalise.
+ * Replaces: `X.astype(float32)` feed + Flatten + BatchNormalization(inference) of
+ * TfFeedForward (examples/models/image_classification/TfFeedForward.py:95,147-148).
+ *   y[i, j] = x[i, j] * scale[j] + shift[j]      (scale/shift NULL: plain cast)
+ * x: uint8 [n, d] row-major.  y: out_dtype [n, ld_out] row-major, ld_out >= d, columns
+ * d..ld_out-1 are written as zero.  scale, shift: float [d] device arrays.
+ */
+int rfk_decode_u8(const uint8_t* x, void* y, int64_t n, int d, int ld_out, const float* scale,
+                  const float* shift, int out_dtype, void* stream);
+
+/*
+ * Follow-on row of SURVEY.md 8(f)3 -- Pillow NEAREST resize folded into the decode.
+ * Replaces: ModelDatasetUtils.resize_as_images (rafiki/model/dataset.py:68-78) + the
+ * decode above.  x: uint8 [n, s_in, s_in, ch]; y: [n, ld_out] with d = s_out*s_out*ch.
+ * Source index = floor((dst + 0.5) * s_in / s_out) per axis (Pillow 5.3.0 default).
+ * out_dtype may also be -1 for a uint8 result (resize only; scale/shift ignored).
+ */
+int rfk_resize_decode_u8(const uint8_t* x, void* y, int64_t n, int s_in, int s_out, int ch,
+                         int ld_out, const float* scale, const float* shift, int out_dtype,
+                         void* stream);
+
+/*
+ * Kernel 2 -- the trial network.
+ * Replaces: the Keras graph of TfFeedForward._build_model run by Model.predict
+ * (TfFeedForward.py:95,141-157) and its load_parameters (TfFeedForward.py:118-135).
+ *
+ * rfk_mlp_create packs one trial on the CURRENT device.  All array arguments are HOST
+ * pointers.  kernels[i] is the Keras Dense kernel of layer i, row-major [in, out];
+ * layers 0..n_hidden-1 are ReLU layers of units[i] outputs, layer n_hidden is the
+ * softmax layer with n_classes outputs.  bn_* are the BatchNormalization vectors [d].
+ * compute_dtype selects the arithmetic (RFK_F32 / RFK_BF16).  Synchronous.
+ */
+int rfk_mlp_create(rfk_mlp_t** out, int d, int n_hidden, const int* units, int n_classes,
+                   const float* const* kernels, const float* const* biases, const float* bn_gamma,
+                   const float* bn_beta, const float* bn_mean, const float* bn_var, float bn_eps,
+                   int compute_dtype);
+int rfk_mlp_destroy(rfk_mlp_t* h);
+
+/* Describe a packed trial: out[0..5] = d, n_hidden, n_classes, compute_dtype,
+ * 1 if the single-kernel fused path applies, widest hidden layer. */
+int rfk_mlp_info(const rfk_mlp_t* h, int* out6);
+
+/* Scratch bytes rfk_mlp_forward needs for a batch of n queries (0 when the fused
+ * single-kernel path applies). */
+int rfk_mlp_workspace_bytes(const rfk_mlp_t* h, int64_t n, size_t* out);
+
+/*
+ * probs[n, n_classes] (float, row-major) = softmax(MLP(BN(x))) for x: uint8 [n, d].
+ * `workspace` is caller-owned device scratch of at least rfk_mlp_workspace_bytes(h, n)
+ * bytes (may be NULL when that is 0), 256-byte aligned.
+ */
+int rfk_mlp_forward(rfk_mlp_t* h, const uint8_t* x, int64_t n, float* probs, void* workspace,
+                    size_t workspace_bytes, void* stream);
+
+/*
+ * Kernel 3 -- cross-trial probability averaging.
+ * Replaces: ensemble_predictions, IMAGE_CLASSIFICATION branch
+ * (rafiki/predictor/ensemble.py:10-14): out[i, :] = mean over trials of probs_w[i, :].
+ * probs: HOST array of w DEVICE pointers, each float [n, c] (pointers may be peer-GPU
+ * memory mapped into this process).  The sum runs in float64 in trial order and is
+ * rounded once to float, so out equals float32(reference mean) bit for bit.
+ */
+int rfk_ensemble_mean(const float* const* probs, int w, int64_t n, int c, float* out, void* stream);
+
+/*
+ * Kernels 1+2+3 for trials that live on one GPU: every trial's forward pass and the
+ * averaging, x read once.  Replaces Predictor.predict's fan-out / gather / ensemble
+ * (rafiki/predictor/predictor.py:35-70) when the workers share a device.
+ * trials: HOST array of w handles created on the current device with the same d and
+ * n_classes.  `scale` multiplies the mean's divisor: out = sum_w probs_w / (w * scale_div)
+ * with scale_div = 1 for a complete ensemble; a rank that holds only part of a larger
+ * ensemble passes total_trials so that partial results add up across ranks.
+ */
+int rfk_ensemble_workspace_bytes(rfk_mlp_t* const* trials, int w, int64_t n, size_t* out);
+int rfk_ensemble_forward(rfk_mlp_t* const* trials, int w, int total_trials, const uint8_t* x,
+                         int64_t n, float* out, void* workspace, size_t workspace_bytes,
+                         void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RAFIKI_B200_H */

@@ -1,0 +1,238 @@
+// Kernel 1: uint8 query decode + BatchNormalization affine, with Pillow-NEAREST resize.
+//
+// Replaces the float feed, Flatten and BatchNormalization(inference) of the Keras graph
+// (examples/models/image_classification/TfFeedForward.py:95,147-148) and, for the resize
+// variant, ModelDatasetUtils.resize_as_images (rafiki/model/dataset.py:68-78).
+//
+// HBM-bound byte work: algorithmic traffic is d * (1 + sizeof(out)) bytes per query.
+// Design: persistent CTAs (a multiple of the SM count), the per-feature scale/shift
+// vectors staged once per CTA in shared memory, one 16-byte load (16 pixels) per thread
+// per step, 16-byte stores, streaming cache hints on both sides.
+#include "rfk_common.cuh"
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kMaxSmemFeatures = 12288;  // 2 * 12288 * 4 B = 96 KB of staged scale/shift
+
+__device__ __forceinline__ uint4 ld_stream_16(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ void st_stream_16(void* p, uint4 v) {
+  asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y),
+               "r"(v.z), "r"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+__device__ __forceinline__ float byte_to_float(uint32_t word, int i) {
+  return (float)((word >> (8 * i)) & 0xffu);
+}
+
+template <typename Out>
+__device__ __forceinline__ void store_one(Out* p, float v);
+template <>
+__device__ __forceinline__ void store_one<float>(float* p, float v) { *p = v; }
+template <>
+__device__ __forceinline__ void store_one<__nv_bfloat16>(__nv_bfloat16* p, float v) {
+  *p = __float2bfloat16_rn(v);
+}
+
+// Fast path: d % 16 == 0, ld_out == d, 16-byte aligned pointers.  One thread = 16 pixels of
+// one row.  `affine` selects the BN multiply-add.
+template <typename Out, bool kAffine>
+__global__ void __launch_bounds__(kThreads)
+decode_vec16_kernel(const uint8_t* __restrict__ x, Out* __restrict__ y, int64_t n_chunks,
+                    int chunks_per_row, const float* __restrict__ scale,
+                    const float* __restrict__ shift, int d, int use_smem) {
+  extern __shared__ __align__(16) float s_aff[];  // [2*d] when use_smem
+  const float* sc = scale;
+  const float* sh = shift;
+  if (kAffine && use_smem) {
+    for (int i = threadIdx.x; i < d; i += kThreads) {
+      s_aff[i] = scale[i];
+      s_aff[d + i] = shift[i];
+    }
+    __syncthreads();
+    sc = s_aff;
+    sh = s_aff + d;
+  }
+  const int64_t stride = (int64_t)gridDim.x * kThreads;
+  for (int64_t c = (int64_t)blockIdx.x * kThreads + threadIdx.x; c < n_chunks; c += stride) {
+    const uint4 raw = ld_stream_16(x + c * 16);
+    const int j0 = (int)(c % chunks_per_row) * 16;
+    const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+    float v[16];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      float4 a = make_float4(1.f, 1.f, 1.f, 1.f), b = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (kAffine) {
+        a = *reinterpret_cast<const float4*>(sc + j0 + 4 * q);
+        b = *reinterpret_cast<const float4*>(sh + j0 + 4 * q);
+      }
+      const float f0 = byte_to_float(w[q], 0), f1 = byte_to_float(w[q], 1);
+      const float f2 = byte_to_float(w[q], 2), f3 = byte_to_float(w[q], 3);
+      v[4 * q + 0] = kAffine ? fmaf(f0, a.x, b.x) : f0;
+      v[4 * q + 1] = kAffine ? fmaf(f1, a.y, b.y) : f1;
+      v[4 * q + 2] = kAffine ? fmaf(f2, a.z, b.z) : f2;
+      v[4 * q + 3] = kAffine ? fmaf(f3, a.w, b.w) : f3;
+    }
+    if (sizeof(Out) == 2) {
+      uint4 o0, o1;
+      o0.x = pack_bf16(v[0], v[1]);   o0.y = pack_bf16(v[2], v[3]);
+      o0.z = pack_bf16(v[4], v[5]);   o0.w = pack_bf16(v[6], v[7]);
+      o1.x = pack_bf16(v[8], v[9]);   o1.y = pack_bf16(v[10], v[11]);
+      o1.z = pack_bf16(v[12], v[13]); o1.w = pack_bf16(v[14], v[15]);
+      char* dst = reinterpret_cast<char*>(y) + c * 32;
+      st_stream_16(dst, o0);
+      st_stream_16(dst + 16, o1);
+    } else {
+      char* dst = reinterpret_cast<char*>(y) + c * 64;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        uint4 o;
+        o.x = __float_as_uint(v[4 * q + 0]); o.y = __float_as_uint(v[4 * q + 1]);
+        o.z = __float_as_uint(v[4 * q + 2]); o.w = __float_as_uint(v[4 * q + 3]);
+        st_stream_16(dst + 16 * q, o);
+      }
+    }
+  }
+}
+
+// General path: any d / ld_out / resize.  One thread per output element; the source index
+// of the NEAREST resize is floor((dst + 0.5) * s_in / s_out) per axis, evaluated in exact
+// integer arithmetic as ((2*dst + 1) * s_in) / (2 * s_out).
+template <typename Out>
+__global__ void __launch_bounds__(kThreads)
+decode_general_kernel(const uint8_t* __restrict__ x, Out* __restrict__ y, int64_t n, int d,
+                      int ld_out, const float* __restrict__ scale, const float* __restrict__ shift,
+                      int s_in, int s_out, int ch) {
+  const int64_t total = n * (int64_t)ld_out;
+  const int64_t stride = (int64_t)gridDim.x * kThreads;
+  const int64_t d_in = s_in > 0 ? (int64_t)s_in * s_in * ch : d;
+  for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < total; i += stride) {
+    const int64_t row = i / ld_out;
+    const int j = (int)(i - row * ld_out);
+    float v = 0.f;
+    if (j < d) {
+      int64_t src = j;
+      if (s_in > 0) {
+        const int c = j % ch;
+        const int px = (j / ch) % s_out;
+        const int py = j / (ch * s_out);
+        const int sx = min(((2 * px + 1) * s_in) / (2 * s_out), s_in - 1);
+        const int sy = min(((2 * py + 1) * s_in) / (2 * s_out), s_in - 1);
+        src = ((int64_t)sy * s_in + sx) * ch + c;
+      }
+      v = (float)x[row * d_in + src];
+      if (scale != nullptr) v = fmaf(v, scale[j], shift[j]);
+    }
+    store_one<Out>(y + i, v);
+  }
+}
+
+__global__ void __launch_bounds__(kThreads)
+resize_u8_kernel(const uint8_t* __restrict__ x, uint8_t* __restrict__ y, int64_t n, int ld_out,
+                 int s_in, int s_out, int ch) {
+  const int d = s_out * s_out * ch;
+  const int64_t total = n * (int64_t)ld_out;
+  const int64_t stride = (int64_t)gridDim.x * kThreads;
+  const int64_t d_in = (int64_t)s_in * s_in * ch;
+  for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < total; i += stride) {
+    const int64_t row = i / ld_out;
+    const int j = (int)(i - row * ld_out);
+    uint8_t v = 0;
+    if (j < d) {
+      const int c = j % ch;
+      const int px = (j / ch) % s_out;
+      const int py = j / (ch * s_out);
+      const int sx = min(((2 * px + 1) * s_in) / (2 * s_out), s_in - 1);
+      const int sy = min(((2 * py + 1) * s_in) / (2 * s_out), s_in - 1);
+      v = x[row * d_in + ((int64_t)sy * s_in + sx) * ch + c];
+    }
+    y[i] = v;
+  }
+}
+
+template <typename Out>
+int launch_decode(const uint8_t* x, Out* y, int64_t n, int d, int ld_out, const float* scale,
+                  const float* shift, int s_in, int s_out, int ch, cudaStream_t st) {
+  const int sms = rfk::num_sms();
+  const bool aligned = ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y)) & 15) == 0 &&
+                       (scale == nullptr ||
+                        ((reinterpret_cast<uintptr_t>(scale) | reinterpret_cast<uintptr_t>(shift)) & 15) == 0);
+  if (s_in <= 0 && d % 16 == 0 && ld_out == d && aligned) {
+    const int64_t n_chunks = n * (int64_t)(d / 16);
+    const int64_t want = (n_chunks + kThreads - 1) / kThreads;
+    const int grid = (int)(want < (int64_t)sms * 8 ? (want > 0 ? want : 1) : (int64_t)sms * 8);
+    const int use_smem = (scale != nullptr && d <= kMaxSmemFeatures) ? 1 : 0;
+    const size_t smem = use_smem ? (size_t)2 * d * sizeof(float) : 0;
+    if (scale != nullptr) {
+      auto k = decode_vec16_kernel<Out, true>;
+      if (smem > 48 * 1024)
+        RFK_CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      k<<<grid, kThreads, smem, st>>>(x, y, n_chunks, d / 16, scale, shift, d, use_smem);
+    } else {
+      decode_vec16_kernel<Out, false><<<grid, kThreads, 0, st>>>(x, y, n_chunks, d / 16, nullptr,
+                                                                nullptr, d, 0);
+    }
+    RFK_LAUNCH_CHECK("decode_vec16_kernel");
+    return RFK_OK;
+  }
+  const int64_t total = n * (int64_t)ld_out;
+  const int64_t want = (total + kThreads - 1) / kThreads;
+  const int grid = (int)(want < (int64_t)sms * 16 ? (want > 0 ? want : 1) : (int64_t)sms * 16);
+  decode_general_kernel<Out><<<grid, kThreads, 0, st>>>(x, y, n, d, ld_out, scale, shift, s_in, s_out, ch);
+  RFK_LAUNCH_CHECK("decode_general_kernel");
+  return RFK_OK;
+}
+
+int decode_dispatch(const uint8_t* x, void* y, int64_t n, int d, int ld_out, const float* scale,
+                    const float* shift, int out_dtype, int s_in, int s_out, int ch, void* stream) {
+  RFK_REQUIRE(n >= 0 && d > 0 && ld_out >= d, "decode: bad shape n=%lld d=%d ld_out=%d", (long long)n, d, ld_out);
+  RFK_REQUIRE((scale == nullptr) == (shift == nullptr), "decode: scale and shift must both be given or both NULL");
+  if (n == 0) return RFK_OK;
+  RFK_REQUIRE(x != nullptr && y != nullptr, "decode: NULL buffer");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (out_dtype == RFK_F32)
+    return launch_decode<float>(x, static_cast<float*>(y), n, d, ld_out, scale, shift, s_in, s_out, ch, st);
+  if (out_dtype == RFK_BF16)
+    return launch_decode<__nv_bfloat16>(x, static_cast<__nv_bfloat16*>(y), n, d, ld_out, scale, shift, s_in, s_out, ch, st);
+  rfk::set_error("decode: unknown out_dtype %d", out_dtype);
+  return RFK_ERR_INVALID;
+}
+
+}  // namespace
+
+extern "C" int rfk_decode_u8(const uint8_t* x, void* y, int64_t n, int d, int ld_out,
+                             const float* scale, const float* shift, int out_dtype, void* stream) {
+  return decode_dispatch(x, y, n, d, ld_out, scale, shift, out_dtype, 0, 0, 1, stream);
+}
+
+extern "C" int rfk_resize_decode_u8(const uint8_t* x, void* y, int64_t n, int s_in, int s_out, int ch,
+                                    int ld_out, const float* scale, const float* shift, int out_dtype,
+                                    void* stream) {
+  RFK_REQUIRE(s_in > 0 && s_out > 0 && ch > 0, "resize: bad sizes s_in=%d s_out=%d ch=%d", s_in, s_out, ch);
+  const int d = s_out * s_out * ch;
+  if (out_dtype == -1) {
+    RFK_REQUIRE(n >= 0 && ld_out >= d, "resize: bad shape");
+    if (n == 0) return RFK_OK;
+    RFK_REQUIRE(x != nullptr && y != nullptr, "resize: NULL buffer");
+    const int64_t total = n * (int64_t)ld_out;
+    const int64_t want = (total + kThreads - 1) / kThreads;
+    const int sms = rfk::num_sms();
+    const int grid = (int)(want < (int64_t)sms * 16 ? (want > 0 ? want : 1) : (int64_t)sms * 16);
+    resize_u8_kernel<<<grid, kThreads, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+        x, static_cast<uint8_t*>(y), n, ld_out, s_in, s_out, ch);
+    RFK_LAUNCH_CHECK("resize_u8_kernel");
+    return RFK_OK;
+  }
+  return decode_dispatch(x, y, n, d, ld_out, scale, shift, out_dtype, s_in, s_out, ch, stream);
+}

@@ -1,0 +1,30 @@
+// Internal entry points shared between the translation units of librafiki_b200.
+#pragma once
+#include "rfk_common.cuh"
+
+namespace rfk {
+
+// mlp_f32.cu -- fp32 CUDA-core path
+size_t mlp_f32_workspace_bytes(const rfk_mlp* h, int64_t n);
+int mlp_f32_forward(rfk_mlp* h, const uint8_t* x, int64_t n, float* probs, void* ws, size_t ws_bytes,
+                    cudaStream_t st);
+
+// gemm_tc.cu -- layered tcgen05 path (decode -> GEMM+bias+ReLU ... -> GEMM+bias+softmax)
+int tc_prepare(rfk_mlp* h);
+void tc_release(rfk_mlp* h);
+size_t tc_workspace_bytes(const rfk_mlp* h, int64_t n);
+int tc_forward(rfk_mlp* h, const uint8_t* x, int64_t n, float* probs, void* ws, size_t ws_bytes,
+               cudaStream_t st);
+
+// fused_trial.cu -- single-kernel tcgen05 path for TfFeedForward-shaped trials
+bool fused_applicable(const rfk_mlp* h);
+int fused_prepare(rfk_mlp* h);
+void fused_release(rfk_mlp* h);
+// out = sum_w probs_w / total_trials over the w trials given (w == total_trials: the mean)
+int fused_forward(rfk_mlp* const* trials, int w, int total_trials, const uint8_t* x, int64_t n,
+                  float* out, cudaStream_t st);
+
+// ensemble.cu
+int scale_inplace(float* p, int64_t count, double divisor, cudaStream_t st);
+
+}  // namespace rfk

@@ -1,0 +1,251 @@
+"""Host runtime of the serving path: packed trials, single-GPU ensembles, pinned-host pipeline.
+
+PyTorch is plumbing here (device memory, streams, pinned buffers); every arithmetic step is a
+call into ``librafiki_b200.so`` through ``_native``.  Nothing in this module computes on the
+CPU and nothing falls back to torch ops: without the CUDA library, construction fails.
+
+Mapping to the reference:
+
+* :class:`Trial`      -- what ``InferenceWorker._load_model`` builds (rafiki/worker/inference.py:78-93):
+  one trial's network, ready to answer batches.
+* :class:`Ensemble`   -- the ``Predictor`` fan-out/gather/mean (rafiki/predictor/predictor.py:35-70)
+  for trials that share a GPU: one fused kernel launch per batch.
+* :class:`HostPipeline` -- the Redis hand-off (rafiki/cache/cache.py:36-63) replaced by pinned host
+  buffers with async H2D / D2H copies on a copy stream pair.
+"""
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _native
+
+COMPUTE = {'f32': _native.RFK_F32, 'fp32': _native.RFK_F32, 'bf16': _native.RFK_BF16}
+
+
+def _require_cuda():
+    if not torch.cuda.is_available():
+        raise RuntimeError('rafiki_b200 needs a CUDA device (sm_100a); there is no CPU fallback')
+
+
+def _stream_ptr(stream=None):
+    s = torch.cuda.current_stream() if stream is None else stream
+    return ctypes.c_void_p(s.cuda_stream)
+
+
+def _check_queries(x, d):
+    if not (isinstance(x, torch.Tensor) and x.is_cuda and x.dtype == torch.uint8):
+        raise TypeError('queries must be a CUDA uint8 tensor')
+    if not x.is_contiguous():
+        raise ValueError('queries must be contiguous')
+    n = x.shape[0]
+    if x.numel() != n * d:
+        raise ValueError('queries have {} features per row, the trial expects {}'.format(
+            x.numel() // max(n, 1), d))
+    return n
+
+
+class _Workspace:
+    """Grow-only device scratch owned by an engine object."""
+
+    def __init__(self, device):
+        self.device = device
+        self.buf = None
+
+    def get(self, nbytes):
+        if nbytes == 0:
+            return ctypes.c_void_p(0), 0
+        if self.buf is None or self.buf.numel() < nbytes:
+            self.buf = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
+        return ctypes.c_void_p(self.buf.data_ptr()), self.buf.numel()
+
+
+class Trial:
+    """One packed trial (TfFeedForward network) on one GPU."""
+
+    def __init__(self, params, compute='bf16', device=None):
+        _require_cuda()
+        self._lib = _native.load()
+        self.device = torch.device('cuda', torch.cuda.current_device() if device is None else
+                                   torch.device(device).index or 0)
+        self.compute = compute
+        with torch.cuda.device(self.device):
+            self.handle = _native.mlp_create(params, COMPUTE[compute])
+        info = _native.mlp_info(self.handle)
+        self.d = info['d']
+        self.n_classes = info['n_classes']
+        self.fused = info['fused']
+        self._ws = _Workspace(self.device)
+
+    def workspace_bytes(self, n):
+        out = ctypes.c_size_t()
+        _native.check(self._lib.rfk_mlp_workspace_bytes(self.handle, n, ctypes.byref(out)))
+        return out.value
+
+    def forward(self, x, out=None, stream=None):
+        """``uint8 [n, ...]`` CUDA tensor -> ``float32 [n, C]`` class probabilities."""
+        if self.handle is None:
+            raise RuntimeError('trial was destroyed')
+        n = _check_queries(x, self.d)
+        if out is None:
+            out = torch.empty((n, self.n_classes), dtype=torch.float32, device=self.device)
+        ws, ws_bytes = self._ws.get(self.workspace_bytes(n))
+        with torch.cuda.device(self.device):
+            _native.check(self._lib.rfk_mlp_forward(self.handle, x.data_ptr(), n, out.data_ptr(), ws, ws_bytes,
+                                                    _stream_ptr(stream)))
+        return out
+
+    def close(self):
+        if getattr(self, 'handle', None) is not None:
+            self._lib.rfk_mlp_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Ensemble:
+    """W trials on one GPU answering the same batch; the mean is taken on the device."""
+
+    def __init__(self, trials, total_trials=None):
+        if len(trials) == 0 or len(trials) > _native.RFK_MAX_TRIALS:
+            raise ValueError('an ensemble takes 1..{} trials'.format(_native.RFK_MAX_TRIALS))
+        self._lib = _native.load()
+        self.trials = list(trials)
+        self.device = trials[0].device
+        self.d = trials[0].d
+        self.n_classes = trials[0].n_classes
+        self.total_trials = len(trials) if total_trials is None else int(total_trials)
+        self._handles = _native.handle_array([t.handle for t in self.trials])
+        self._ws = _Workspace(self.device)
+        self.fused = all(t.fused for t in self.trials)
+
+    def workspace_bytes(self, n):
+        out = ctypes.c_size_t()
+        _native.check(self._lib.rfk_ensemble_workspace_bytes(self._handles, len(self.trials), n, ctypes.byref(out)))
+        return out.value
+
+    def forward(self, x, out=None, stream=None):
+        n = _check_queries(x, self.d)
+        if out is None:
+            out = torch.empty((n, self.n_classes), dtype=torch.float32, device=self.device)
+        ws, ws_bytes = self._ws.get(self.workspace_bytes(n))
+        with torch.cuda.device(self.device):
+            _native.check(self._lib.rfk_ensemble_forward(self._handles, len(self.trials), self.total_trials,
+                                                         x.data_ptr(), n, out.data_ptr(), ws, ws_bytes,
+                                                         _stream_ptr(stream)))
+        return out
+
+
+def ensemble_mean(probs, out=None, stream=None):
+    """Kernel 3 alone: list of ``float32 [n, C]`` CUDA tensors -> their mean (float64 sum, one rounding)."""
+    lib = _native.load()
+    w = len(probs)
+    n, c = probs[0].shape
+    for p in probs:
+        if not (p.is_cuda and p.dtype == torch.float32 and p.is_contiguous() and tuple(p.shape) == (n, c)):
+            raise ValueError('probs must be contiguous float32 CUDA tensors of one shape')
+    if out is None:
+        out = torch.empty((n, c), dtype=torch.float32, device=probs[0].device)
+    ptrs = (ctypes.c_void_p * w)(*[p.data_ptr() for p in probs])
+    with torch.cuda.device(out.device):
+        _native.check(lib.rfk_ensemble_mean(ptrs, w, n, c, out.data_ptr(), _stream_ptr(stream)))
+    return out
+
+
+def decode_u8(x, scale=None, shift=None, out_dtype=torch.bfloat16, ld_out=None, stream=None):
+    """Kernel 1 alone: ``uint8 [n, d]`` -> ``out_dtype [n, ld_out]`` with the BN affine."""
+    lib = _native.load()
+    n = x.shape[0]
+    d = x.numel() // max(n, 1) if n else int(np.prod(x.shape[1:]))
+    ld = d if ld_out is None else int(ld_out)
+    out = torch.empty((n, ld), dtype=out_dtype, device=x.device)
+    code = {torch.float32: _native.RFK_F32, torch.bfloat16: _native.RFK_BF16}[out_dtype]
+    sp = ctypes.c_void_p(scale.data_ptr()) if scale is not None else ctypes.c_void_p(0)
+    hp = ctypes.c_void_p(shift.data_ptr()) if shift is not None else ctypes.c_void_p(0)
+    with torch.cuda.device(x.device):
+        _native.check(lib.rfk_decode_u8(x.data_ptr(), out.data_ptr(), n, d, ld, sp, hp, code, _stream_ptr(stream)))
+    return out
+
+
+def resize_decode_u8(x, s_out, scale=None, shift=None, out_dtype=torch.uint8, stream=None):
+    """Pillow-NEAREST resize (+ optional decode): ``uint8 [n, s, s(, ch)]`` -> ``[n, s_out*s_out*ch]``."""
+    lib = _native.load()
+    n, s_in = x.shape[0], x.shape[1]
+    ch = x.shape[3] if x.dim() == 4 else 1
+    d = s_out * s_out * ch
+    out = torch.empty((n, d), dtype=out_dtype, device=x.device)
+    code = {torch.uint8: -1, torch.float32: _native.RFK_F32, torch.bfloat16: _native.RFK_BF16}[out_dtype]
+    sp = ctypes.c_void_p(scale.data_ptr()) if scale is not None else ctypes.c_void_p(0)
+    hp = ctypes.c_void_p(shift.data_ptr()) if shift is not None else ctypes.c_void_p(0)
+    with torch.cuda.device(x.device):
+        _native.check(lib.rfk_resize_decode_u8(x.data_ptr(), out.data_ptr(), n, s_in, s_out, ch, d, sp, hp, code,
+                                               _stream_ptr(stream)))
+    return out
+
+
+class HostPipeline:
+    """Pinned-host hand-off around an :class:`Ensemble` (or :class:`Trial`).
+
+    ``serve(batch_u8_numpy) -> float32 numpy [n, C]`` copies the batch from pinned host memory
+    to the device, runs the engine, and copies the probabilities back, all on one stream; with
+    ``depth`` > 1 slots, ``submit``/``collect`` keep several batches in flight so the copies of
+    one batch overlap the kernels of another.
+    """
+
+    def __init__(self, engine, max_batch, depth=2):
+        _require_cuda()
+        self.engine = engine
+        self.device = engine.device
+        self.max_batch = int(max_batch)
+        self.depth = int(depth)
+        d, c = engine.d, engine.n_classes
+        self._slots = []
+        for _ in range(self.depth):
+            self._slots.append({
+                'h_in': torch.empty((self.max_batch, d), dtype=torch.uint8).pin_memory(),
+                'h_out': torch.empty((self.max_batch, c), dtype=torch.float32).pin_memory(),
+                'd_in': torch.empty((self.max_batch, d), dtype=torch.uint8, device=self.device),
+                'd_out': torch.empty((self.max_batch, c), dtype=torch.float32, device=self.device),
+                'stream': torch.cuda.Stream(device=self.device),
+                'done': torch.cuda.Event(),
+                'n': 0,
+            })
+        self._next = 0
+        self.h2d_bytes = 0
+        self.d2h_bytes = 0
+
+    def stage(self, slot_idx, batch):
+        """Copy a ``uint8 [n, d]`` array into the slot's pinned input buffer (host -> host)."""
+        s = self._slots[slot_idx]
+        n = batch.shape[0]
+        if n > self.max_batch:
+            raise ValueError('batch of {} exceeds max_batch {}'.format(n, self.max_batch))
+        s['h_in'][:n].copy_(torch.from_numpy(np.ascontiguousarray(batch).reshape(n, -1)))
+        s['n'] = n
+
+    def launch(self, slot_idx, n=None):
+        """H2D + kernels + D2H of one slot, asynchronously on the slot's stream."""
+        s = self._slots[slot_idx]
+        n = s['n'] if n is None else n
+        s['n'] = n
+        with torch.cuda.stream(s['stream']):
+            s['d_in'][:n].copy_(s['h_in'][:n], non_blocking=True)
+            self.engine.forward(s['d_in'][:n], out=s['d_out'][:n], stream=s['stream'])
+            s['h_out'][:n].copy_(s['d_out'][:n], non_blocking=True)
+            s['done'].record(s['stream'])
+        self.h2d_bytes = n * self.engine.d
+        self.d2h_bytes = n * self.engine.n_classes * 4
+
+    def wait(self, slot_idx):
+        s = self._slots[slot_idx]
+        s['done'].synchronize()
+        return s['h_out'][:s['n']]
+
+    def serve(self, batch):
+        self.stage(0, batch)
+        self.launch(0)
+        return self.wait(0).numpy().copy()

@@ -1,0 +1,241 @@
+"""Parity of the CUDA path (through the C ABI) against the CPU oracle and the reference's
+golden vectors.  Run on the B200 box: ``pytest -m gpu``.
+
+Tolerances (BASELINE.json north_star): probabilities within 2e-3 and argmax identical on
+>= 99.9 % of queries for the bf16 tensor-core path; within 1e-5 for the fp32 path; the
+ensemble mean equals float32(reference) exactly.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import feedforward as ff
+from rafiki_b200 import _native, engine, synth
+
+pytestmark = pytest.mark.gpu
+
+TOL_BF16 = 2e-3
+TOL_F32 = 1e-5
+
+
+@pytest.fixture(scope='module', autouse=True)
+def _device():
+    assert torch.cuda.is_available(), 'GPU tests need a CUDA device'
+    assert _native.load().rfk_device_check(0) == 0, _native.load().rfk_last_error()
+    torch.cuda.set_device(0)
+    yield
+    torch.cuda.synchronize()
+
+
+def _np(t):
+    return t.detach().float().cpu().numpy()
+
+
+# ------------------------------------------------------------------------------- kernel 1
+@pytest.mark.parametrize('n,d', [(1, 784), (333, 784), (4096, 784), (64, 3072), (7, 1024)])
+@pytest.mark.parametrize('out_dtype', [torch.float32, torch.bfloat16])
+def test_decode_affine_vectorised(n, d, out_dtype):
+    rng = np.random.default_rng(n + d)
+    X = rng.integers(0, 256, size=(n, d), dtype=np.uint8)
+    p = synth.make_trial(1, int(round((d if d != 3072 else 1024) ** 0.5)), 3 if d == 3072 else 1, 1, 8,
+                         dead=synth.dead_mask(d))
+    inv, shift = ff.bn_affine(p)
+    want = X.astype(np.float32) * inv + shift
+    got = engine.decode_u8(torch.from_numpy(X).cuda(), torch.from_numpy(inv).cuda(), torch.from_numpy(shift).cuda(),
+                           out_dtype)
+    if out_dtype == torch.float32:
+        # fused multiply-add vs NumPy's multiply-then-add: one rounding apart
+        np.testing.assert_allclose(_np(got), want, rtol=3e-7, atol=1e-6)
+    else:
+        ref = torch.from_numpy(want).to(torch.bfloat16).float().numpy()
+        np.testing.assert_allclose(_np(got), ref, rtol=2 ** -7, atol=1e-6)
+        assert np.mean(_np(got) == ref) > 0.999
+    # plain cast is exact in both dtypes
+    got = engine.decode_u8(torch.from_numpy(X).cuda(), None, None, out_dtype)
+    assert np.array_equal(_np(got), X.astype(np.float32))
+
+
+def test_decode_ragged_and_padded():
+    rng = np.random.default_rng(5)
+    X = rng.integers(0, 256, size=(37, 75), dtype=np.uint8)     # d not a multiple of 16
+    sc = rng.normal(size=75).astype(np.float32)
+    sh = rng.normal(size=75).astype(np.float32)
+    got = engine.decode_u8(torch.from_numpy(X).cuda(), torch.from_numpy(sc).cuda(), torch.from_numpy(sh).cuda(),
+                           torch.float32, ld_out=80)
+    want = np.zeros((37, 80), np.float32)
+    want[:, :75] = X.astype(np.float32) * sc + sh
+    np.testing.assert_allclose(_np(got), want, rtol=3e-7, atol=1e-6)
+    assert engine.decode_u8(torch.empty((0, 784), dtype=torch.uint8, device='cuda')).shape == (0, 784)
+
+
+def test_resize_nearest_matches_reference_golden(golden_dir):
+    g = np.load(os.path.join(golden_dir, 'resize_reference.npz'))
+    x = torch.from_numpy(g['queries']).cuda()
+    got = engine.resize_decode_u8(x, 32)
+    assert np.array_equal(got.cpu().numpy().reshape(-1, 32, 32), g['nearest_32'])
+    assert np.array_equal(engine.resize_decode_u8(x, 28).cpu().numpy().reshape(-1, 28, 28), g['identity_28'])
+    rgb = torch.from_numpy(g['rgb_in']).cuda()
+    assert np.array_equal(engine.resize_decode_u8(rgb, 32).cpu().numpy().reshape(-1, 32, 32, 3), g['rgb_identity_32'])
+    f = engine.resize_decode_u8(x, 32, out_dtype=torch.float32)
+    assert np.array_equal(_np(f).reshape(-1, 32, 32), g['nearest_32'].astype(np.float32))
+
+
+# ------------------------------------------------------------------------------- kernel 3
+@pytest.mark.parametrize('name', ['w1', 'w2', 'w3', 'w8', 'w5c3', 'onehot'])
+def test_ensemble_mean_equals_reference_rounded_once(golden_dir, name):
+    g = np.load(os.path.join(golden_dir, 'ensemble_reference.npz'))
+    p, want = g[name + '_in'], g[name + '_out']
+    got = engine.ensemble_mean([torch.from_numpy(np.ascontiguousarray(q)).cuda() for q in p])
+    assert np.array_equal(got.cpu().numpy(), want.astype(np.float32))
+    assert np.abs(got.cpu().numpy().astype(np.float64) - want).max() <= 1e-6
+
+
+def test_ensemble_mean_large_and_list_api():
+    rng = np.random.default_rng(3)
+    p = rng.random((5, 70001, 10), dtype=np.float32)
+    got = engine.ensemble_mean([torch.from_numpy(q).cuda() for q in p])
+    assert np.array_equal(got.cpu().numpy(), ff.ensemble_mean_array(p).astype(np.float32))
+    from rafiki_b200.predictor.ensemble import ensemble_predictions
+    small = p[:3, :9].tolist()
+    out = ensemble_predictions(small, 'IMAGE_CLASSIFICATION')
+    ref = ff.ensemble_predictions(small, 'IMAGE_CLASSIFICATION')
+    assert isinstance(out, list) and isinstance(out[0][0], float)
+    assert np.array_equal(np.asarray(out), np.asarray(ref).astype(np.float32).astype(np.float64))
+
+
+# ------------------------------------------------------------------------------- kernel 2
+SHAPES = [(28, 1, 2, 128), (28, 1, 1, 36), (28, 1, 2, 7), (32, 1, 2, 36), (28, 1, 1, 2), (28, 1, 2, 100),
+          (28, 1, 1, 128), (32, 3, 2, 64)]
+
+
+def _case(S, ch, L, H, n, t=0, kind='fashion'):
+    d = S * S * ch
+    dead = synth.dead_mask(d)
+    params = synth.make_trial(t, S, ch, L, H, dead=dead, data_kind=kind)
+    X = synth.make_queries(n, S, ch, kind, seed=t, dead=dead)
+    return params, X
+
+
+@pytest.mark.parametrize('S,ch,L,H', SHAPES)
+def test_trial_forward_fp32_path(S, ch, L, H):
+    params, X = _case(S, ch, L, H, 517)
+    tr = engine.Trial(params, compute='f32')
+    got = _np(tr.forward(torch.from_numpy(X).cuda()))
+    want = ff.forward(params, X, np.float32)
+    assert np.abs(got - want).max() <= TOL_F32
+    assert np.abs(got - ff.forward(params, X, np.float64)).max() <= TOL_F32
+    tr.close()
+
+
+@pytest.mark.parametrize('S,ch,L,H', SHAPES)
+@pytest.mark.parametrize('n', [1, 128, 517, 4096])
+def test_trial_forward_tensor_core_path(S, ch, L, H, n):
+    params, X = _case(S, ch, L, H, n)
+    tr = engine.Trial(params, compute='bf16')
+    assert tr.fused
+    got = _np(tr.forward(torch.from_numpy(X).cuda()))
+    want = ff.forward(params, X, np.float32)
+    assert np.isfinite(got).all()
+    assert np.abs(got - want).max() <= TOL_BF16
+    assert np.abs(got.sum(1) - 1).max() <= 1e-5
+    if n >= 4096:
+        assert np.mean(got.argmax(1) == want.argmax(1)) >= 0.999
+    tr.close()
+
+
+def test_sample_query_of_the_reference(golden_dir):
+    q = np.load(os.path.join(golden_dir, 'resize_reference.npz'))['sample_query']
+    g = np.load(os.path.join(golden_dir, 'forward_restatement.npz'))
+    dead = synth.dead_mask(784)
+    for t, (L, H) in enumerate([(2, 128), (1, 36), (2, 7)]):
+        params = synth.make_trial(t, 28, 1, L, H, dead=dead, data_kind='fashion')
+        X = synth.make_queries(16, 28, 1, 'fashion', seed=t, dead=dead)
+        X[0] = q
+        want = g['unpinned_t{}_probs_f64'.format(t)]
+        for compute, tol in (('bf16', TOL_BF16), ('f32', TOL_F32)):
+            tr = engine.Trial(params, compute=compute)
+            assert np.abs(_np(tr.forward(torch.from_numpy(X).cuda())) - want).max() <= tol
+            tr.close()
+
+
+def test_zero_weights_give_uniform_probabilities():
+    params, X = _case(28, 1, 2, 16, 64)
+    params['kernels'] = [np.zeros_like(k) for k in params['kernels']]
+    params['biases'] = [np.zeros_like(b) for b in params['biases']]
+    for compute in ('bf16', 'f32'):
+        tr = engine.Trial(params, compute=compute)
+        assert np.allclose(_np(tr.forward(torch.from_numpy(X).cuda())), 0.1, atol=1e-6)
+        tr.close()
+
+
+# ------------------------------------------------------------------------------- kernels 1+2+3
+@pytest.mark.parametrize('compute,tol', [('bf16', TOL_BF16), ('f32', TOL_F32)])
+@pytest.mark.parametrize('w,n', [(3, 4096), (8, 1000), (2, 129), (1, 64)])
+def test_ensemble_forward(compute, tol, w, n):
+    dead = synth.dead_mask(784)
+    shapes = [(2, 128), (1, 36), (2, 7), (2, 128), (1, 128), (2, 64), (1, 2), (2, 100)]
+    params = [synth.make_trial(t, 28, 1, *shapes[t], dead=dead, data_kind='fashion') for t in range(w)]
+    X = synth.make_queries(n, 28, 1, 'fashion', seed=11, dead=dead)
+    x = torch.from_numpy(X).cuda()
+    trials = [engine.Trial(p, compute=compute) for p in params]
+    ens = engine.Ensemble(trials)
+    got = ens.forward(x).cpu().numpy()
+    want = ff.ensemble_mean_array([ff.forward(p, X, np.float32) for p in params])
+    assert np.abs(got.astype(np.float64) - want).max() <= tol
+    # the fused kernel equals "each trial alone, then kernel 3" bit for bit
+    singles = [t.forward(x) for t in trials]
+    assert np.array_equal(got, engine.ensemble_mean(singles).cpu().numpy())
+    if n >= 4096:
+        assert np.mean(got.argmax(1) == want.argmax(1)) >= 0.999
+    # a rank holding part of a larger ensemble: partial sums add up to the full mean
+    if w >= 2:
+        a = engine.Ensemble(trials[:1], total_trials=w).forward(x).cpu().numpy().astype(np.float64)
+        b = engine.Ensemble(trials[1:], total_trials=w).forward(x).cpu().numpy().astype(np.float64)
+        assert np.abs((a + b) - got).max() <= 1e-6
+    for t in trials:
+        t.close()
+
+
+def test_full_size_properties_batch_65536():
+    """BASELINE config 3 size: size-independent properties instead of an oracle pass."""
+    dead = synth.dead_mask(784)
+    params = [synth.make_trial(t, 28, 1, 2, 128, dead=dead) for t in range(8)]
+    X = synth.make_queries(65536, 28, 1, 'uniform', seed=0, dead=dead)
+    x = torch.from_numpy(X).cuda()
+    trials = [engine.Trial(p) for p in params]
+    out = engine.Ensemble(trials).forward(x)
+    o = out.cpu().numpy()
+    assert np.isfinite(o).all() and np.abs(o.sum(1) - 1).max() <= 1e-5
+    # identical trials ensemble to the trial itself
+    same = engine.Ensemble([trials[0]] * 4).forward(x)
+    assert torch.equal(same, trials[0].forward(x))
+    # rows are independent: any sub-batch gives the same rows, bit for bit
+    part = engine.Ensemble(trials).forward(x[12800:12800 + 4096].contiguous())
+    assert torch.equal(part, out[12800:12800 + 4096])
+    perm = torch.randperm(65536, device='cuda')
+    assert torch.equal(engine.Ensemble(trials).forward(x[perm].contiguous()), out[perm])
+    # oracle on a bounded slice of the same batch
+    sl = slice(60000, 60000 + 2048)
+    want = ff.ensemble_mean_array([ff.forward(p, X[sl], np.float32) for p in params])
+    assert np.abs(o[sl].astype(np.float64) - want).max() <= TOL_BF16
+    assert np.mean(o[sl].argmax(1) == want.argmax(1)) >= 0.999
+    for t in trials:
+        t.close()
+
+
+def test_errors_are_reported_not_swallowed():
+    params, X = _case(28, 1, 1, 8, 4)
+    tr = engine.Trial(params)
+    with pytest.raises(ValueError):
+        tr.forward(torch.zeros((4, 100), dtype=torch.uint8, device='cuda'))
+    with pytest.raises(TypeError):
+        tr.forward(torch.zeros((4, 784), dtype=torch.float32, device='cuda'))
+    other = engine.Trial(synth.make_trial(0, 32, 1, 1, 8))
+    with pytest.raises(_native.RafikiNativeError):
+        engine.Ensemble([tr, other]).forward(torch.from_numpy(X).cuda())
+    bad = dict(params)
+    bad['kernels'] = [params['kernels'][0]] + [np.zeros((9, 10), np.float32)]
+    with pytest.raises(ValueError):
+        engine.Trial(bad)

@@ -1,0 +1,122 @@
+"""The drop-in plugin, worker and predictor on the GPU, against the oracle's composition of the
+reference path (oracle.feedforward.serve_batch / predictor_predict)."""
+import os
+import pickle
+import threading
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import feedforward as ff
+from rafiki_b200 import engine, synth
+from rafiki_b200.cache import Cache
+from rafiki_b200.constants import TaskType
+from rafiki_b200.db import Database
+from rafiki_b200.model import serve_model_class
+from rafiki_b200.predictor import Predictor
+from rafiki_b200.worker import InferenceWorker
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+MODEL_FILE = os.path.join(ROOT, 'examples', 'models', 'image_classification', 'TfFeedForward.py')
+
+
+def _knobs(p):
+    return {'epochs': 1, 'hidden_layer_count': p['hidden_layer_count'], 'hidden_layer_units': p['hidden_layer_units'],
+            'learning_rate': 1e-3, 'batch_size': 32, 'image_size': p['image_size']}
+
+
+def _wire(p):
+    keys = ('image_size', 'bn_gamma', 'bn_beta', 'bn_mean', 'bn_var', 'bn_eps', 'kernels', 'biases')
+    return {k: p[k] for k in keys}
+
+
+@pytest.mark.parametrize('S', [28, 32])
+def test_dropin_model_file_through_the_plugin_harness(S, tmp_path, monkeypatch, golden_dir):
+    monkeypatch.chdir(tmp_path)
+    dead = synth.dead_mask(S * S)
+    p = synth.make_trial(3, S, 1, 2, 36, dead=dead, data_kind='fashion')
+    queries = synth.make_queries(40, 28, 1, 'fashion', seed=2).tolist()     # 28x28 queries, resized when S = 32
+    queries[0] = np.load(os.path.join(golden_dir, 'resize_reference.npz'))['sample_query'].tolist()
+    model, preds = serve_model_class(MODEL_FILE, 'TfFeedForward', TaskType.IMAGE_CLASSIFICATION, _wire(p), queries,
+                                     _knobs(p))
+    want = ff.serve_batch([p], queries)
+    assert isinstance(preds, list) and len(preds) == 40 and len(preds[0]) == 10 and isinstance(preds[0][0], float)
+    assert np.abs(np.asarray(preds) - np.asarray(want)).max() <= 2e-3
+    again = pickle.loads(pickle.dumps(model.dump_parameters()))
+    assert np.array_equal(again['kernels'][0], p['kernels'][0])
+    model.destroy()
+
+
+def test_fp32_mode_of_the_dropin(tmp_path, monkeypatch):
+    monkeypatch.chdir(tmp_path)
+    monkeypatch.setenv('RAFIKI_B200_COMPUTE', 'f32')
+    p = synth.make_trial(4, 28, 1, 1, 100)
+    queries = synth.make_queries(33).tolist()
+    model, preds = serve_model_class(MODEL_FILE, 'TfFeedForward', TaskType.IMAGE_CLASSIFICATION, _wire(p), queries,
+                                     _knobs(p))
+    assert np.abs(np.asarray(preds) - np.asarray(ff.serve_batch([p], queries))).max() <= 1e-5
+    model.destroy()
+
+
+def test_worker_predictor_ensemble_on_gpu(tmp_path, monkeypatch):
+    monkeypatch.chdir(tmp_path)
+    dead = synth.dead_mask(784)
+    params = [synth.make_trial(t, 28, 1, L, H, dead=dead, data_kind='fashion')
+              for t, (L, H) in enumerate([(2, 128), (1, 36), (2, 7)])]
+    db, cache = Database(), Cache()
+    task = TaskType.IMAGE_CLASSIFICATION
+    model = db.create_model(open(MODEL_FILE, 'rb').read(), 'TfFeedForward', task)
+    tj = db.create_train_job(task)
+    stj = db.create_sub_train_job(tj.id, model.id)
+    ij = db.create_inference_job(tj.id, 'predictor-svc')
+    workers = []
+    for i, p in enumerate(params):
+        path = tmp_path / 'trial{}.model'.format(i)
+        path.write_bytes(pickle.dumps(_wire(p)))
+        trial = db.create_trial(stj.id, _knobs(p), str(path))
+        db.create_inference_job_worker('worker-{}'.format(i), ij.id, trial.id)
+        workers.append(InferenceWorker('worker-{}'.format(i), cache=cache, db=db, batch_size=64))
+    threads = [threading.Thread(target=w.start, daemon=True) for w in workers]
+    for t in threads:
+        t.start()
+    pred = Predictor('predictor-svc', db=db, cache=cache)
+    pred.start()
+    for _ in range(3000):
+        if len(cache.get_workers_of_inference_job(ij.id)) == 3:
+            break
+        threading.Event().wait(0.01)
+    queries = synth.make_queries(150, 28, 1, 'fashion', seed=5, dead=dead).tolist()
+    one = pred.predict(queries[0])
+    want_one = ff.predictor_predict(params, queries[0])
+    assert sorted(one) == ['prediction'] and len(one['prediction']) == 10
+    assert np.abs(np.asarray(one['prediction']) - np.asarray(want_one['prediction'])).max() <= 2e-3
+    got = pred.predict_batch(queries)['predictions']
+    want = ff.serve_batch(params, queries)
+    assert np.abs(np.asarray(got) - np.asarray(want)).max() <= 2e-3
+    # co-located trials: the predictor answers the batch with one fused launch
+    trials = [engine.Trial(p) for p in params]
+    pred.attach_ensemble(engine.Ensemble(trials), max_batch=128)
+    fused = pred.predict_batch(queries)['predictions']
+    assert np.abs(np.asarray(fused) - np.asarray(want)).max() <= 2e-3
+    assert np.abs(np.asarray(fused) - np.asarray(got)).max() <= 1e-6
+    for w in workers:
+        w.stop()
+    for t in threads:
+        t.join(5)
+
+
+def test_host_pipeline_overlapped_slots():
+    dead = synth.dead_mask(784)
+    params = [synth.make_trial(t, 28, 1, 2, 64, dead=dead) for t in range(3)]
+    trials = [engine.Trial(p) for p in params]
+    pipe = engine.HostPipeline(engine.Ensemble(trials), max_batch=512, depth=3)
+    batches = [synth.make_queries(512 - 17 * i, 28, 1, 'uniform', seed=i, dead=dead) for i in range(3)]
+    for i, b in enumerate(batches):
+        pipe.stage(i, b)
+        pipe.launch(i)
+    for i, b in enumerate(batches):
+        got = pipe.wait(i).numpy()
+        want = ff.ensemble_mean_array([ff.forward(p, b, np.float32) for p in params])
+        assert got.shape == (len(b), 10) and np.abs(got - want).max() <= 2e-3
