@@ -1,0 +1,313 @@
+#!/usr/bin/env python
+"""Benchmark of the serving hot path (BASELINE.json metric: ensemble queries/sec at 1/2/4/8 B200).
+
+    python bench.py --gpus N --steps K --warmup W [--workload c3|c2] [--impl reference]
+
+prints ONE JSON line (rank 0).  A step is one pass of the hot path over one batch of synthetic
+queries: uint8 images in, ensemble-mean class probabilities out.
+
+Workloads (BASELINE.json `configs`):
+  c3 (default)  8-trial TfFeedForward ensemble (D 784, H 128, L 2), batch 65536 -- the
+                configuration the north_star's targets are quoted on; it fits one GPU.  At N GPUs
+                the 8 trials are placed 8/N per GPU (one per GPU at N = 8), every GPU sees the whole
+                batch, and the partial means are summed onto rank 0 by an NCCL reduce: strong scaling.
+  c2            3-trial ensemble, batch 4096 per GPU; N > 1 runs independent replicas (weak scaling).
+
+`value` is device-resident throughput (queries already in HBM); `e2e` goes through the pinned-host
+pipeline (H2D of the uint8 batch and D2H of the probabilities inside the timed region).  The
+`cpu_baseline` leg and `--impl reference` time the CPU oracle (`oracle/`, a NumPy restatement of
+the reference's TensorFlow-1.12 path, which cannot be installed here) on the box's host cores.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+WORKLOADS = {
+    'c3': dict(trials=8, batch=65536, image_size=28, channels=1, hidden=128, layers=2, scaling='strong',
+               name='8-trial TfFeedForward ensemble, 28x28, batch 65536 (BASELINE configs[2])'),
+    'c2': dict(trials=3, batch=4096, image_size=28, channels=1, hidden=128, layers=2, scaling='weak',
+               name='3-trial TfFeedForward ensemble, 28x28, batch 4096 per GPU (BASELINE configs[1])'),
+}
+L2_BYTES = 126 * 1024 * 1024
+FALLBACK_PEAKS = {'hbm_gbs': 6650.0, 'bf16_tflops': 1590.0, 'bf16_tflops_sustained': 1400.0}
+
+
+def load_peaks():
+    path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        p['_source'] = 'measured (MEASURED_PEAKS.json)'
+        return p
+    p = dict(FALLBACK_PEAKS)
+    p['_source'] = 'fallback (B200_PROFILING.md)'
+    return p
+
+
+def make_workload(wl, rng_seed=0, n_batches=None):
+    from rafiki_b200 import synth
+    d = wl['image_size'] ** 2 * wl['channels']
+    dead = synth.dead_mask(d)
+    params = [synth.make_trial(t, wl['image_size'], wl['channels'], wl['layers'], wl['hidden'], dead=dead)
+              for t in range(wl['trials'])]
+    if n_batches is None:   # enough distinct batches that the rotation exceeds L2
+        n_batches = max(2, -(-int(1.6 * L2_BYTES) // (wl['batch'] * d)))
+    batches = [synth.make_queries(wl['batch'], wl['image_size'], wl['channels'], 'uniform', seed=rng_seed + i,
+                                  dead=dead).reshape(wl['batch'], d) for i in range(n_batches)]
+    return params, batches, d
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
+    QUERY = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+             'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index = index
+        self.samples = []
+        self._halt = threading.Event()
+
+    def run(self):
+        while not self._halt.is_set():
+            try:
+                out = subprocess.run(['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.QUERY,
+                                      '--format=csv,noheader,nounits'], capture_output=True, text=True, timeout=5)
+                parts = [x.strip() for x in out.stdout.strip().split(',')]
+                if len(parts) >= 6:
+                    self.samples.append(parts)
+            except Exception:
+                pass
+            self._halt.wait(0.2)
+
+    def stop(self):
+        self._halt.set()
+        self.join(3)
+        sm = [float(s[0]) for s in self.samples if s[0].replace('.', '', 1).isdigit()]
+        mx = [float(s[1]) for s in self.samples if s[1].replace('.', '', 1).isdigit()]
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        reasons = [n for i, n in enumerate(names) if any(s[2 + i].lower().startswith('active') for s in self.samples)]
+        return {'sm_mhz': statistics.median(sm) if sm else None, 'sm_max_mhz': max(mx) if mx else None,
+                'reasons': reasons, 'samples': len(self.samples)}
+
+
+def cpu_oracle_rate(params, batch, sample, repeats, threads):
+    """queries/s of the CPU oracle (list in, list out, exactly the reference's composition) on the
+    first `sample` queries of the batch."""
+    from oracle import feedforward as ff     # the one place bench.py executes oracle/
+    from threadpoolctl import threadpool_limits
+    side = int(round((batch.shape[1]) ** 0.5))
+    queries = batch[:sample].reshape(sample, side, side).tolist()
+    times = []
+    with threadpool_limits(limits=threads):
+        for _ in range(repeats):
+            t0 = time.perf_counter()
+            out = ff.serve_batch(params, queries)
+            times.append(time.perf_counter() - t0)
+    assert len(out) == sample
+    return sample / min(times), times
+
+
+def run_reference(args, wl):
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return 0
+    params, batches, d = make_workload(wl, n_batches=1)
+    cores = os.cpu_count() or 1
+    sample = min(wl['batch'], 512)     # bounded per-step sample: ~0.4 s of CPU work per step
+    for _ in range(max(args.warmup, 1) if args.warmup < 3 else 1):
+        cpu_oracle_rate(params, batches[0], min(sample, 256), 1, cores)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        cpu_oracle_rate(params, batches[0], sample, 1, cores)
+    dt = time.perf_counter() - t0
+    value = sample * args.steps / dt
+    line = {
+        'impl': 'reference', 'metric': 'ensemble_queries_per_sec', 'value': value, 'unit': 'queries/s',
+        'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': dt / args.steps * 1e3,
+        'higher_is_better': True, 'scaling': wl['scaling'], 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+        'config': {'workload': wl['name'], 'trials': wl['trials'], 'batch': wl['batch'],
+                   'note': 'CPU oracle port of the reference path (TensorFlow 1.12 not installable); '
+                           'each step = first {} queries of the batch, list in / list out'.format(sample)},
+        'cpu_baseline': {'value': value, 'unit': 'queries/s', 'cores': cores, 'kind': 'port',
+                         'sample': '{} queries x {} trials per step'.format(sample, wl['trials'])},
+        'e2e': {'value': value, 'unit': 'queries/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+        'gpu_launches': 0,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=200)
+    ap.add_argument('--warmup', type=int, default=10)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--workload', default='c3', choices=sorted(WORKLOADS))
+    ap.add_argument('--compute', default='f16', choices=['f16', 'bf16', 'f32'])
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    args = ap.parse_args()
+    wl = WORKLOADS[args.workload]
+    if args.impl == 'reference':
+        return run_reference(args, wl)
+
+    import torch
+    import torch.distributed as dist
+    from rafiki_b200 import engine, synth
+
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    rank = int(os.environ.get('RANK', '0'))
+    local_rank = int(os.environ.get('LOCAL_RANK', '0'))
+    if args.gpus != world:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit('launch with torchrun --nproc-per-node {} for --gpus {}'.format(args.gpus, args.gpus))
+    if not torch.cuda.is_available():
+        raise SystemExit('bench.py needs a GPU (no CPU fallback)')
+    torch.cuda.set_device(local_rank)
+    dev = torch.device('cuda', local_rank)
+    if world > 1:
+        os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+        dist.init_process_group('nccl', device_id=dev)
+
+    params, batches, d = make_workload(wl)
+    n, W, C = wl['batch'], wl['trials'], synth.NUM_CLASSES
+    if wl['scaling'] == 'strong':      # trials dealt round-robin to ranks; every rank sees the whole batch
+        mine = [t for t in range(W) if t % world == rank]
+    else:                              # independent replicas
+        mine = list(range(W))
+    trials = [engine.Trial(params[t], compute=args.compute) for t in mine]
+    ens = engine.Ensemble(trials, total_trials=W) if trials else None
+    xs = [torch.from_numpy(b).to(dev) for b in batches]
+    out = torch.zeros((n, C), dtype=torch.float32, device=dev)
+    do_reduce = world > 1 and wl['scaling'] == 'strong'
+
+    def step(i):
+        if ens is not None:
+            ens.forward(xs[i % len(xs)], out=out)
+        if do_reduce:
+            dist.reduce(out, dst=0, op=dist.ReduceOp.SUM)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(max(args.warmup, 3)):
+        step(i)
+    barrier()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        step(i)
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    units = n * args.steps * (world if wl['scaling'] == 'weak' else 1)
+    value = units / (ms * 1e-3)
+
+    # ---- end to end: pinned host -> device -> pinned host, three batches in flight
+    e2e = None
+    if ens is not None:
+        depth = 3
+        pipe = engine.HostPipeline(ens, max_batch=n, depth=depth)
+        for s in range(depth):
+            pipe.stage(s, batches[s % len(batches)])
+        for i in range(3):
+            pipe.launch(i % depth)
+            pipe.wait(i % depth)
+        barrier()
+        e2e_steps = max(4, min(args.steps, 40))
+        t0 = time.perf_counter()
+        inflight = []
+        for i in range(e2e_steps):
+            s = i % depth
+            if len(inflight) == depth:
+                pipe.wait(inflight.pop(0))
+            pipe.launch(s)
+            inflight.append(s)
+        for s in inflight:
+            pipe.wait(s)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        if world > 1:
+            t = torch.tensor([dt], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt = float(t.item())
+        e_units = n * e2e_steps * (world if wl['scaling'] == 'weak' else 1)
+        e2e = {'value': e_units / dt, 'unit': 'queries/s', 'h2d_bytes_per_step': pipe.h2d_bytes,
+               'd2h_bytes_per_step': pipe.d2h_bytes, 'steps': e2e_steps, 'slots_in_flight': depth,
+               'note': 'per rank: H2D of the whole uint8 batch + fused kernel + D2H of the probabilities'
+                       + ('; cross-rank reduce not included' if do_reduce else '')}
+    clocks = sampler.stop() if sampler else None
+
+    if rank == 0:
+        peaks = load_peaks()
+        flops_per_query_local = sum(synth.trial_flops_per_query(params[t]) for t in mine)
+        flops_per_launch = flops_per_query_local * n
+        ms_launch = ms / args.steps
+        achieved = flops_per_launch / (ms_launch * 1e-3) / 1e12
+        peak = float(peaks.get('bf16_tflops_sustained', FALLBACK_PEAKS['bf16_tflops_sustained']))
+        traffic = None
+        summ = os.path.join(ROOT, 'profiles', 'ncu_summary.json')
+        if os.path.exists(summ):
+            try:
+                traffic = json.load(open(summ)).get(args.workload, {}).get('fused_dram_bytes_per_launch')
+            except Exception:
+                traffic = None
+        line = {
+            'metric': 'ensemble_queries_per_sec', 'value': value, 'unit': 'queries/s', 'n_gpus': world,
+            'steps': args.steps, 'warmup': max(args.warmup, 3), 'ms_per_step': ms / args.steps,
+            'higher_is_better': True, 'scaling': wl['scaling'], 'vs_baseline': None, 'dtype': args.compute,
+            'data': 'synthetic',
+            'config': {'workload': wl['name'], 'trials': W, 'batch': n, 'd': d, 'hidden_units': wl['hidden'],
+                       'hidden_layers': wl['layers'], 'classes': C,
+                       'parallelism': ('trial-per-gpu x{} + nccl reduce'.format(world) if do_reduce else
+                                       ('replicas x{}'.format(world) if world > 1 else 'single gpu, fused ensemble')),
+                       'l2': 'rotating over {} distinct resident batches ({} MB > L2)'.format(
+                           len(xs), len(xs) * n * d // (1 << 20))},
+            'clocks': clocks,
+            'e2e': e2e,
+            'gpu_launches': args.steps * (1 if ens is not None else 0),
+            'roofline': {'bound': 'tensor', 'achieved': achieved, 'peak': peak, 'unit': 'TFLOP/s',
+                         'frac': achieved / peak, 'traffic': traffic,
+                         'kernel': 'fused_ensemble_kernel (one launch per step; duration = timed region / steps)',
+                         'peak_source': peaks['_source'] + ', bf16_tflops_sustained (same rate for fp16)',
+                         'flops_per_launch': flops_per_launch,
+                         'hbm_gbs_algorithmic': n * (d + 4 * C) / (ms_launch * 1e-3) / 1e9},
+        }
+        if not args.no_cpu_baseline:
+            cores = os.cpu_count() or 1
+            sample = min(n, 4096)
+            rate, times = cpu_oracle_rate(params, batches[0], sample, 2, cores)
+            line['cpu_baseline'] = {'value': rate, 'unit': 'queries/s', 'cores': cores, 'kind': 'port',
+                                    'sample': 'first {} queries of batch 0 x {} trials, best of 2 ({:.1f} s each); '
+                                              'NumPy restatement of the TF-1.12 path, list in / list out'.format(
+                                                  sample, W, min(times))}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == '__main__':
+    sys.exit(main())

@@ -6,8 +6,8 @@ underneath:
 
 * ``predict`` (``:89-97``): the queries are resized exactly as ``dataset_utils.resize_as_images``
   does, uploaded as uint8 and pushed through ``librafiki_b200`` (decode + BatchNormalization +
-  Dense/ReLU layers + softmax on tcgen05 tensor cores, or true fp32 with
-  ``RAFIKI_B200_COMPUTE=f32``); the result is ``probs.tolist()`` as before.
+  Dense/ReLU layers + softmax on tcgen05 tensor cores with fp16 operands, or true fp32 with
+  ``RAFIKI_B200_COMPUTE=f32``, or bf16 operands with ``=bf16``); the result is ``probs.tolist()`` as before.
 * ``dump_parameters`` / ``load_parameters`` (``:102-135``): the dict holds the Keras tensors as
   raw arrays (Dense kernels ``[in, out]``, biases, BatchNormalization gamma / beta / moving mean /
   moving variance) instead of a base64 HDF5 file, because neither TensorFlow nor h5py exists on
@@ -50,7 +50,7 @@ class TfFeedForward(BaseModel):
         self._knobs = knobs
         self._params = None
         self._trial = None
-        self._compute = os.environ.get('RAFIKI_B200_COMPUTE', 'bf16')
+        self._compute = os.environ.get('RAFIKI_B200_COMPUTE', 'f16')
 
     # ------------------------------------------------------------------ serving path
     def predict(self, queries):

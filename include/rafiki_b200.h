@@ -37,6 +37,9 @@ extern "C" {
 
 #define RFK_F32 0  /* fp32 CUDA-core arithmetic (parity path, <= 1e-5 of the oracle) */
 #define RFK_BF16 1 /* bf16 operands on tcgen05 tensor cores, fp32 accumulate */
+#define RFK_F16 2  /* fp16 operands on tcgen05 tensor cores, fp32 accumulate: same speed as
+                      RFK_BF16, 8x finer operand rounding (11-bit significand); weights must
+                      stay below 65504 in magnitude, hidden activations saturate there */
 
 #define RFK_MAX_TRIALS 32  /* most trials one ensemble call accepts */
 #define RFK_MAX_CLASSES 16 /* most classes the fused kernels accept */
@@ -80,7 +83,7 @@ int rfk_resize_decode_u8(const uint8_t* x, void* y, int64_t n, int s_in, int s_o
  * pointers.  kernels[i] is the Keras Dense kernel of layer i, row-major [in, out];
  * layers 0..n_hidden-1 are ReLU layers of units[i] outputs, layer n_hidden is the
  * softmax layer with n_classes outputs.  bn_* are the BatchNormalization vectors [d].
- * compute_dtype selects the arithmetic (RFK_F32 / RFK_BF16).  Synchronous.
+ * compute_dtype selects the arithmetic (RFK_F32 / RFK_BF16 / RFK_F16).  Synchronous.
  */
 int rfk_mlp_create(rfk_mlp_t** out, int d, int n_hidden, const int* units, int n_classes,
                    const float* const* kernels, const float* const* biases, const float* bn_gamma,
@@ -119,9 +122,9 @@ int rfk_ensemble_mean(const float* const* probs, int w, int64_t n, int c, float*
  * averaging, x read once.  Replaces Predictor.predict's fan-out / gather / ensemble
  * (rafiki/predictor/predictor.py:35-70) when the workers share a device.
  * trials: HOST array of w handles created on the current device with the same d and
- * n_classes.  `scale` multiplies the mean's divisor: out = sum_w probs_w / (w * scale_div)
- * with scale_div = 1 for a complete ensemble; a rank that holds only part of a larger
- * ensemble passes total_trials so that partial results add up across ranks.
+ * n_classes.  out = sum over the w given trials of probs_w / total_trials: a complete
+ * ensemble passes total_trials = w (the mean); a rank that holds only part of a larger
+ * ensemble passes the full trial count so that partial results add up across ranks.
  */
 int rfk_ensemble_workspace_bytes(rfk_mlp_t* const* trials, int w, int64_t n, size_t* out);
 int rfk_ensemble_forward(rfk_mlp_t* const* trials, int w, int total_trials, const uint8_t* x,

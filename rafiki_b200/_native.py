@@ -10,10 +10,11 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, 'librafiki_b200.so')
+LIB_PATH = os.environ.get('RFK_LIB', os.path.join(_HERE, 'librafiki_b200.so'))   # RFK_LIB: development override
 
 RFK_F32 = 0
 RFK_BF16 = 1
+RFK_F16 = 2
 RFK_MAX_TRIALS = 32
 RFK_MAX_CLASSES = 16
 

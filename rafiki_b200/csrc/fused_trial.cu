@@ -12,23 +12,29 @@
 // algorithmic minimum, d bytes in + 4*C bytes out per query, at which point the work
 // is bound by the tensor pipe (236 kflop per 824 bytes for D 784, H 128, L 2).
 //
-// Structure (one persistent CTA per SM, 352 threads, warp-specialised):
+// Structure (one persistent CTA per SM, 480 threads, warp-specialised):
 //   warps 0-3  epilogue   TMEM -> registers, bias + ReLU -> bf16 hidden tile in shared memory
 //                         (the next layer's A operand); last layer: bias + softmax, and the
 //                         running ensemble sum in float64 registers; final store of the mean
-//   warps 4-7  A producer 16-byte loads of the uint8 tile, exact uint8 -> bf16 conversion,
-//                         stores in the K-major 128B-swizzled layout tcgen05.mma reads
-//   warp 8     W1 loader  cp.async.bulk (TMA engine) of the pre-swizzled first-layer weight
+//   warps 4-11 A producer 16-byte loads of the uint8 tile (six pipeline steps of loads in
+//                         flight per thread, ~48 KB per SM, to cover HBM latency), exact
+//                         uint8 -> fp16/bf16 conversion, stores in the K-major 128B-swizzled
+//                         layout tcgen05.mma reads
+//   warp 12    W1 loader  cp.async.bulk (TMA engine) of the pre-swizzled first-layer weight
 //                         blocks into a 4-stage ring shared with the A producer
-//   warp 9     MMA issuer one thread issues every tcgen05.mma; accumulators live in TMEM
+//   warp 13    MMA issuer one thread issues every tcgen05.mma; accumulators live in TMEM
 //                         (2 x 128 columns for layer 1, double buffered so the epilogue of one
 //                         item overlaps the MMAs of the next, 128 for layer 2, 16 for layer 3)
-//   warp 10    parameter loader  cp.async.bulk of W2, W3 and the biases of the item's trial
+//   warp 14    parameter loader  cp.async.bulk of W2, W3 and the biases of the item's trial
 // A work item is (tile of 128 queries, trial); items of one tile run back to back so the tile
 // stays hot in L1/L2 and the ensemble sum never leaves registers.
 //
 // BatchNormalization is folded into the first layer at pack time (mlp.cu), so the A operand
-// is the raw pixel value, which bf16 holds exactly.
+// is the raw pixel value, which fp16 and bf16 both hold exactly.  Operands are fp16 (RFK_F16,
+// the default: 11-bit significands keep the probabilities within 2e-3 of the fp32 oracle) or
+// bf16 (RFK_BF16); accumulation is fp32 in TMEM either way.
+#include <stdlib.h>
+
 #include "pack.cuh"
 #include "rfk_internal.cuh"
 #include "sm100.cuh"
@@ -63,10 +69,11 @@ constexpr int OFF_TMEM_SLOT = OFF_BAR + NUM_BARS * 8;
 constexpr int SMEM_USED = OFF_TMEM_SLOT + 16;
 constexpr int SMEM_BYTES = SMEM_USED + 1024;      // slack for the 1024-byte alignment of the base
 
-constexpr int kEpiWarps = 4, kProdWarps = 4;
-constexpr int kProdThreads = kProdWarps * 32;
-constexpr int kThreads = (kEpiWarps + kProdWarps + 3) * 32;   // 352
-constexpr int WARP_W1 = 8, WARP_MMA = 9, WARP_PAR = 10;
+constexpr int kEpiWarps = 4, kProdWarps = 8;
+constexpr int kProdThreads = kProdWarps * 32;                 // 256: two 16-byte pieces per thread per step
+constexpr int kPrefetch = 6;                                  // pipeline steps of x loads in flight per thread
+constexpr int kThreads = (kEpiWarps + kProdWarps + 3) * 32;   // 480
+constexpr int WARP_W1 = kEpiWarps + kProdWarps, WARP_MMA = WARP_W1 + 1, WARP_PAR = WARP_W1 + 2;
 
 constexpr int TMEM_COLS = 512;
 constexpr int COL_ACC1 = 0;     // two buffers of 128 columns
@@ -90,6 +97,8 @@ struct FusedParams {
   float* out;
   long long n;
   int d, n_kb, w, total_trials, n_classes, n_tiles;
+  long long* prof;   // development only (RFK_FUSED_PROF): PF_COUNT counters, summed over CTAs
+  int debug;   // development only (RFK_FUSED_DEBUG): 1 skip W1 copies, 2 skip x loads/stores, 4 skip layer-1 MMAs
 };
 
 struct Bars {
@@ -108,15 +117,37 @@ __device__ __forceinline__ uint32_t u8x2_to_bf16x2(uint32_t word, int e0) {
   return __byte_perm(__float_as_uint(f0), __float_as_uint(f1), 0x7632u);
 }
 
-__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+// exact uint8 -> fp16: 0x6400 | b is the half 1024 + b (ulp 1 in [1024, 2048)); subtract 1024.
+__device__ __forceinline__ uint32_t u8x2_to_f16x2(uint32_t word, int e0) {
+  const uint32_t biased = __byte_perm(word, 0x64646464u, 0x4040u | (uint32_t)e0 | ((uint32_t)(e0 + 1) << 8));
   uint32_t r;
-  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  asm("sub.rn.f16x2 %0, %1, %2;" : "=r"(r) : "r"(biased), "r"(0x64006400u));
+  return r;
+}
+template <bool kF16>
+__device__ __forceinline__ uint32_t u8x2_to_op(uint32_t word, int e0) {
+  return kF16 ? u8x2_to_f16x2(word, e0) : u8x2_to_bf16x2(word, e0);
+}
+
+// two fp32 -> packed 16-bit operand pair (lo in the low half); fp16 saturates at +-65504
+template <bool kF16>
+__device__ __forceinline__ uint32_t pack_op_x2(float lo, float hi) {
+  uint32_t r;
+  if (kF16) {
+    lo = fminf(lo, 65504.f);
+    hi = fminf(hi, 65504.f);
+    asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  } else {
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  }
   return r;
 }
 
 __device__ __forceinline__ uint4 ldg_u4(const uint8_t* p) {
   uint4 r;
-  asm volatile("ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
   return r;
 }
 
@@ -125,31 +156,69 @@ __device__ __forceinline__ void sts_u4(uint32_t addr, uint4 v) {
                : "memory");
 }
 
-// TMEM accumulator row -> bias + ReLU -> bf16 -> hidden tile (A operand of the next layer)
+// TMEM accumulator row -> bias + ReLU -> 16-bit -> hidden tile (A operand of the next layer).
+// Two 16-column TMEM loads are issued before the wait, 32 columns per iteration.
+template <bool kF16>
 __device__ __forceinline__ void epilogue_hidden(uint32_t tmem_row_addr, int width, const float* bias,
                                                 uint32_t hid_base, int row) {
   const uint32_t row_off = (uint32_t)row * 128u;
   const uint32_t sw = (uint32_t)(row & 7);
-  for (int c0 = 0; c0 < width; c0 += 16) {
-    uint32_t v[16];
-    tmem_ld16(tmem_row_addr + (uint32_t)c0, v);
+  for (int c0 = 0; c0 < width; c0 += 32) {
+    uint32_t v[2][16];
+    const bool two = c0 + 16 < width;
+    tmem_ld16(tmem_row_addr + (uint32_t)c0, v[0]);
+    if (two) tmem_ld16(tmem_row_addr + (uint32_t)c0 + 16u, v[1]);
     tmem_ld_wait();
-    uint32_t p[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const float a = fmaxf(__uint_as_float(v[2 * j]) + bias[c0 + 2 * j], 0.f);
-      const float b = fmaxf(__uint_as_float(v[2 * j + 1]) + bias[c0 + 2 * j + 1], 0.f);
-      p[j] = pack_bf16x2(a, b);
+    for (int half = 0; half < 2; ++half) {
+      if (half == 1 && !two) break;
+      const int c = c0 + 16 * half;
+      const float4* b4 = reinterpret_cast<const float4*>(bias + c);
+      uint32_t p[8];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float4 bb = b4[j];
+        const float a0 = fmaxf(__uint_as_float(v[half][4 * j + 0]) + bb.x, 0.f);
+        const float a1 = fmaxf(__uint_as_float(v[half][4 * j + 1]) + bb.y, 0.f);
+        const float a2 = fmaxf(__uint_as_float(v[half][4 * j + 2]) + bb.z, 0.f);
+        const float a3 = fmaxf(__uint_as_float(v[half][4 * j + 3]) + bb.w, 0.f);
+        p[2 * j] = pack_op_x2<kF16>(a0, a1);
+        p[2 * j + 1] = pack_op_x2<kF16>(a2, a3);
+      }
+      const uint32_t atom = hid_base + (uint32_t)(c >> 6) * HID_ATOM + row_off;
+      const uint32_t ch = (uint32_t)((c & 63) >> 3);
+      sts_u4(atom + (((ch) ^ sw) << 4), make_uint4(p[0], p[1], p[2], p[3]));
+      sts_u4(atom + (((ch + 1) ^ sw) << 4), make_uint4(p[4], p[5], p[6], p[7]));
     }
-    const uint32_t atom = hid_base + (uint32_t)(c0 >> 6) * HID_ATOM + row_off;
-    const uint32_t ch = (uint32_t)((c0 & 63) >> 3);
-    sts_u4(atom + (((ch) ^ sw) << 4), make_uint4(p[0], p[1], p[2], p[3]));
-    sts_u4(atom + (((ch + 1) ^ sw) << 4), make_uint4(p[4], p[5], p[6], p[7]));
   }
 }
 
+// kProf (development, RFK_FUSED_PROF=1): the leader thread of each warp role accumulates the
+// cycles it spends blocked on each kind of barrier and adds them to P.prof at exit.
+enum ProfSlot { PF_EPI_BIAS, PF_EPI_ACC1, PF_EPI_ACC2, PF_EPI_ACC3, PF_EPI_TOTAL, PF_PROD_EMPTY, PF_PROD_TOTAL,
+                PF_W1_EMPTY, PF_PAR_BIAS_FREE, PF_PAR_W23_FREE, PF_MMA_ACC1_EMPTY, PF_MMA_FULL, PF_MMA_W23_FULL,
+                PF_MMA_HID_L2, PF_MMA_HID_L3, PF_MMA_TOTAL, PF_MMA_ISSUE_L1, PF_MMA_COMMIT_L1, PF_MMA_FENCE, PF_COUNT };
+
+template <bool kProf>
+__device__ __forceinline__ void wait_prof(uint64_t* bar, uint32_t parity, long long (&prof)[PF_COUNT], int slot) {
+  if (kProf) {
+    const long long t0 = clock64();
+    mbar_wait(bar, parity);
+    prof[slot] += clock64() - t0;
+  } else {
+    mbar_wait(bar, parity);
+  }
+}
+
+template <bool kF16, bool kProf>
 __global__ void __launch_bounds__(kThreads, 1)
 fused_ensemble_kernel(const __grid_constant__ FusedParams P) {
+  long long prof[PF_COUNT];
+  if (kProf) {
+#pragma unroll
+    for (int i = 0; i < PF_COUNT; ++i) prof[i] = 0;
+  }
+  const long long t_start = kProf ? clock64() : 0;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   Bars* bars = reinterpret_cast<Bars*>(smem + OFF_BAR);
@@ -179,7 +248,14 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P) {
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
-  const uint32_t tmem_base = *tmem_slot;
+  // The kernel owns all 512 TMEM columns of its SM (one CTA per SM), so the allocation starts at
+  // column 0, lane 0.  Using the literal 0 keeps every TMEM address warp-uniform for the compiler
+  // (a value read back from shared memory is not, and costs a serialising loop around each MMA).
+  if (*tmem_slot != 0u) {
+    if (threadIdx.x == 0) printf("rafiki_b200: unexpected TMEM base %u\n", *tmem_slot);
+    __trap();
+  }
+  constexpr uint32_t tmem_base = 0u;
 
   const int n_kb = P.n_kb;
   const int w = P.w;
@@ -194,6 +270,7 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P) {
 #pragma unroll
     for (int j = 0; j < CPAD; ++j) acc[j] = 0.0;
     int item = 0;
+    uint32_t acc2_phase = 0;          // acc2_full completes one phase per two-hidden-layer item only
     for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
       for (int t = 0; t < w; ++t, ++item) {
         const TrialDev& T = P.trial[t];
@@ -201,26 +278,27 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P) {
         const uint32_t par2 = (uint32_t)((item >> 1) & 1);
         const uint32_t par1 = (uint32_t)(item & 1);
         const float* bias = reinterpret_cast<const float*>(smem + OFF_BIAS + buf * BIAS_BYTES);
-        mbar_wait(&bars->bias_full[buf], par2);
+        wait_prof<kProf>(&bars->bias_full[buf], par2, prof, PF_EPI_BIAS);
         // ---- layer 1: acc1[buf] -> hidden
-        mbar_wait(&bars->acc1_full[buf], par2);
+        wait_prof<kProf>(&bars->acc1_full[buf], par2, prof, PF_EPI_ACC1);
         tc_fence_after_sync();
-        epilogue_hidden(lane_addr + COL_ACC1 + buf * HMAX, T.h1_pad, bias, hid_base, row);
+        epilogue_hidden<kF16>(lane_addr + COL_ACC1 + buf * HMAX, T.h1_pad, bias, hid_base, row);
         tc_fence_before_sync();
         mbar_arrive(&bars->acc1_empty[buf]);
         fence_proxy_async_smem();
         mbar_arrive(&bars->hid_ready);
         // ---- layer 2 (two-hidden-layer trials): acc2 -> hidden
         if (T.n_hidden == 2) {
-          mbar_wait(&bars->acc2_full, par1);
+          wait_prof<kProf>(&bars->acc2_full, acc2_phase, prof, PF_EPI_ACC2);
+          acc2_phase ^= 1u;
           tc_fence_after_sync();
-          epilogue_hidden(lane_addr + COL_ACC2, T.h2_pad, bias + HMAX, hid_base, row);
+          epilogue_hidden<kF16>(lane_addr + COL_ACC2, T.h2_pad, bias + HMAX, hid_base, row);
           tc_fence_before_sync();
           fence_proxy_async_smem();
           mbar_arrive(&bars->hid_ready);
         }
         // ---- softmax layer: acc3 -> probabilities -> running ensemble sum
-        mbar_wait(&bars->acc3_full, par1);
+        wait_prof<kProf>(&bars->acc3_full, par1, prof, PF_EPI_ACC3);
         tc_fence_after_sync();
         uint32_t v[16];
         tmem_ld16(lane_addr + COL_ACC3, v);
@@ -256,52 +334,58 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P) {
     }
   } else if (warp < kEpiWarps + kProdWarps) {
     // =============================================================== A producer warps
-    const int tp = threadIdx.x - kEpiWarps * 32;                 // 0..127
+    // A pipeline step is one 64-wide K block of one item: 128 rows x 64 bytes of uint8.  Each of
+    // the 256 threads owns two 16-byte pieces of it (rows r_in and r_in + 64, quarter q) and
+    // keeps kPrefetch steps of loads in flight in a register ring.
+    const int tp = threadIdx.x - kEpiWarps * 32;                 // 0..255
     const int q = tp & 3;                                        // 16-byte quarter of the 64-byte row chunk
-    const int r_in = tp >> 2;                                    // 0..31
+    const int r_in = tp >> 2;                                    // 0..63
     const uint32_t a_base = smem_base + OFF_A;
-    int stage = 0;
-    uint32_t phase = 0;
     const int d = P.d;
-    // register double buffering: the loads of step s+1 are in flight while step s is converted
-    uint4 cur[4], nxt[4];
-    auto load_step = [&](int tile, int kb, uint4 (&dst)[4]) {
-      const long long row0 = (long long)tile * TILE_M;
-      const int k = kb * KB + q * 16;
+    int my_tiles = 0;
+    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) ++my_tiles;
+    const int total_steps = my_tiles * w * n_kb;
+    uint4 ring[kPrefetch][2];
+    // load cursor
+    int l_tile = blockIdx.x, l_t = 0, l_kb = 0, l_step = 0;
+    auto load_next = [&](uint4 (&dst)[2]) {
+      if (l_step < total_steps) {
+        const long long row0 = (long long)l_tile * TILE_M;
+        const int k = l_kb * KB + q * 16;
 #pragma unroll
-      for (int it = 0; it < 4; ++it) {
-        const long long grow = row0 + it * 32 + r_in;
-        dst[it] = (grow < P.n && k < d) ? ldg_u4(P.x + grow * d + k) : make_uint4(0u, 0u, 0u, 0u);
-      }
-    };
-    // flattened step cursor for the prefetch: (tile, t, kb)
-    int l_tile = blockIdx.x, l_t = 0, l_kb = 0;
-    auto advance_load = [&]() {
-      if (++l_kb == n_kb) {
-        l_kb = 0;
-        if (++l_t == w) {
-          l_t = 0;
-          l_tile += gridDim.x;
+        for (int it = 0; it < 2; ++it) {
+          const long long grow = row0 + it * 64 + r_in;
+          dst[it] = (grow < P.n && k < d && !(P.debug & 2)) ? ldg_u4(P.x + grow * d + k) : make_uint4(0u, 0u, 0u, 0u);
+        }
+        ++l_step;
+        if (++l_kb == n_kb) {
+          l_kb = 0;
+          if (++l_t == w) {
+            l_t = 0;
+            l_tile += gridDim.x;
+          }
         }
       }
     };
-    if (l_tile < P.n_tiles) load_step(l_tile, l_kb, cur);
-    advance_load();
-    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
-      for (int t = 0; t < w; ++t) {
-        for (int kb = 0; kb < n_kb; ++kb) {
-          if (l_tile < P.n_tiles) load_step(l_tile, l_kb, nxt);
-          advance_load();
-          mbar_wait(&bars->empty[stage], phase ^ 1u);
+#pragma unroll
+    for (int j = 0; j < kPrefetch; ++j) load_next(ring[j]);
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int s0 = 0; s0 < total_steps; s0 += kPrefetch) {
+#pragma unroll
+      for (int j = 0; j < kPrefetch; ++j) {
+        if (s0 + j < total_steps) {
+          wait_prof<kProf>(&bars->empty[stage], phase ^ 1u, prof, PF_PROD_EMPTY);
           const uint32_t st_base = a_base + (uint32_t)stage * A_STAGE;
 #pragma unroll
-          for (int it = 0; it < 4; ++it) {
-            const int row = it * 32 + r_in;
-            const uint4 raw = cur[it];
-            const uint4 lo = make_uint4(u8x2_to_bf16x2(raw.x, 0), u8x2_to_bf16x2(raw.x, 2),
-                                        u8x2_to_bf16x2(raw.y, 0), u8x2_to_bf16x2(raw.y, 2));
-            const uint4 hi = make_uint4(u8x2_to_bf16x2(raw.z, 0), u8x2_to_bf16x2(raw.z, 2),
-                                        u8x2_to_bf16x2(raw.w, 0), u8x2_to_bf16x2(raw.w, 2));
+          for (int it = 0; it < 2; ++it) {
+            if (P.debug & 2) break;
+            const int row = it * 64 + r_in;
+            const uint4 raw = ring[j][it];
+            const uint4 lo = make_uint4(u8x2_to_op<kF16>(raw.x, 0), u8x2_to_op<kF16>(raw.x, 2),
+                                        u8x2_to_op<kF16>(raw.y, 0), u8x2_to_op<kF16>(raw.y, 2));
+            const uint4 hi = make_uint4(u8x2_to_op<kF16>(raw.z, 0), u8x2_to_op<kF16>(raw.z, 2),
+                                        u8x2_to_op<kF16>(raw.w, 0), u8x2_to_op<kF16>(raw.w, 2));
             const uint32_t rbase = st_base + (uint32_t)row * 128u;
             const uint32_t sw = (uint32_t)(row & 7);
             sts_u4(rbase + ((((uint32_t)(2 * q)) ^ sw) << 4), lo);
@@ -309,129 +393,172 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P) {
           }
           fence_proxy_async_smem();
           mbar_arrive(&bars->full[stage]);
-#pragma unroll
-          for (int it = 0; it < 4; ++it) cur[it] = nxt[it];
+          load_next(ring[j]);
           if (++stage == STAGES) { stage = 0; phase ^= 1u; }
         }
       }
     }
   } else if (warp == WARP_W1) {
     // =============================================================== first-layer weight loader
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
-        for (int t = 0; t < w; ++t) {
-          const TrialDev& T = P.trial[t];
-          const uint32_t bytes = (uint32_t)T.h1_pad * 128u;
-          for (int kb = 0; kb < n_kb; ++kb) {
-            mbar_wait(&bars->empty[stage], phase ^ 1u);
-            mbar_arrive_expect_tx(&bars->full[stage], bytes);
-            bulk_g2s(smem + OFF_B + stage * B_STAGE, T.w1 + (size_t)kb * bytes, bytes, &bars->full[stage]);
-            if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+    // The whole warp runs the loop (warp-uniform control flow keeps addresses in uniform
+    // registers); lane 0 alone issues the copies.
+    int stage = 0;
+    uint32_t phase = 0;
+#ifdef RFK_LOADER_SINGLE
+    if (lane == 0)
+#endif
+    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
+      for (int t = 0; t < w; ++t) {
+        const TrialDev& T = P.trial[t];
+        const uint32_t bytes = (uint32_t)T.h1_pad * 128u;
+        const uint8_t* src = T.w1;
+        for (int kb = 0; kb < n_kb; ++kb) {
+          wait_prof<kProf>(&bars->empty[stage], phase ^ 1u, prof, PF_W1_EMPTY);
+          if (lane == 0) {
+            if (P.debug & 1) {
+              mbar_arrive(&bars->full[stage]);
+            } else {
+              mbar_arrive_expect_tx(&bars->full[stage], bytes);
+              bulk_g2s(smem + OFF_B + stage * B_STAGE, src + (size_t)kb * bytes, bytes, &bars->full[stage]);
+            }
           }
+#ifndef RFK_LOADER_SINGLE
+          __syncwarp();
+#endif
+          if (++stage == STAGES) { stage = 0; phase ^= 1u; }
         }
       }
     }
   } else if (warp == WARP_PAR) {
     // =============================================================== per-trial parameter loader
-    if (lane == 0) {
-      int item = 0;
-      for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
-        for (int t = 0; t < w; ++t, ++item) {
-          const TrialDev& T = P.trial[t];
-          const int buf = item & 1;
-          mbar_wait(&bars->bias_free[buf], (uint32_t)(((item >> 1) & 1) ^ 1));
+    int item = 0;
+#ifdef RFK_LOADER_SINGLE
+    if (lane == 0)
+#endif
+    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
+      for (int t = 0; t < w; ++t, ++item) {
+        const TrialDev& T = P.trial[t];
+        const int buf = item & 1;
+        wait_prof<kProf>(&bars->bias_free[buf], (uint32_t)(((item >> 1) & 1) ^ 1), prof, PF_PAR_BIAS_FREE);
+        if (lane == 0) {
           mbar_arrive_expect_tx(&bars->bias_full[buf], BIAS_BYTES);
           bulk_g2s(smem + OFF_BIAS + buf * BIAS_BYTES, T.bias, BIAS_BYTES, &bars->bias_full[buf]);
-          mbar_wait(&bars->w23_free, (uint32_t)((item & 1) ^ 1));
-          const int hl_pad = T.n_hidden == 2 ? T.h2_pad : T.h1_pad;
-          const uint32_t w3_bytes = (uint32_t)((hl_pad + 63) / 64) * CPAD * 128u;
-          const uint32_t w2_bytes = T.n_hidden == 2 ? (uint32_t)((T.h1_pad + 63) / 64) * (uint32_t)T.h2_pad * 128u : 0u;
+        }
+#ifndef RFK_LOADER_SINGLE
+        __syncwarp();
+#endif
+        wait_prof<kProf>(&bars->w23_free, (uint32_t)((item & 1) ^ 1), prof, PF_PAR_W23_FREE);
+        const int hl_pad = T.n_hidden == 2 ? T.h2_pad : T.h1_pad;
+        const uint32_t w3_bytes = (uint32_t)((hl_pad + 63) / 64) * CPAD * 128u;
+        const uint32_t w2_bytes = T.n_hidden == 2 ? (uint32_t)((T.h1_pad + 63) / 64) * (uint32_t)T.h2_pad * 128u : 0u;
+        if (lane == 0) {
           mbar_arrive_expect_tx(&bars->w23_full, w2_bytes + w3_bytes);
           if (w2_bytes) bulk_g2s(smem + OFF_W2, T.w2, w2_bytes, &bars->w23_full);
           bulk_g2s(smem + OFF_W3, T.w3, w3_bytes, &bars->w23_full);
         }
+#ifndef RFK_LOADER_SINGLE
+        __syncwarp();
+#endif
       }
     }
   } else if (warp == WARP_MMA) {
-    // =============================================================== MMA issuer (one thread)
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0, hid_phase = 0;
-      const uint32_t a_base = smem_base + OFF_A, b_base = smem_base + OFF_B;
-      const uint32_t hid_base = smem_base + OFF_HID, w2_base = smem_base + OFF_W2, w3_base = smem_base + OFF_W3;
-      // layers 2/3 of a finished layer-1 item still to be issued: pend 1 = layer 2 next, 2 = layer 3 next
-      int pend = 0, pend_item = 0, pend_t = 0;
-      auto issue_layer2 = [&]() {
-        const TrialDev& T = P.trial[pend_t];
-        mbar_wait(&bars->w23_full, (uint32_t)(pend_item & 1));
-        mbar_wait(&bars->hid_ready, hid_phase);
-        hid_phase ^= 1u;
-        tc_fence_after_sync();
-        const uint32_t idesc = idesc_bf16_f32(TILE_M, T.h2_pad);
-        const int ksteps = T.h1_pad / 16;
-        for (int k = 0; k < ksteps; ++k) {
-          const uint32_t a = hid_base + (uint32_t)(k >> 2) * HID_ATOM + (uint32_t)(k & 3) * 32u;
-          const uint32_t b = w2_base + (uint32_t)(k >> 2) * ((uint32_t)T.h2_pad * 128u) + (uint32_t)(k & 3) * 32u;
-          mma_bf16_ss(tmem_base + COL_ACC2, smem_desc_sw128(a), smem_desc_sw128(b), idesc, k > 0);
-        }
-        mma_commit(&bars->acc2_full);
-        pend = 2;
-      };
-      auto issue_layer3 = [&]() {
-        const TrialDev& T = P.trial[pend_t];
-        if (T.n_hidden != 2) mbar_wait(&bars->w23_full, (uint32_t)(pend_item & 1));
-        mbar_wait(&bars->hid_ready, hid_phase);
-        hid_phase ^= 1u;
-        tc_fence_after_sync();
-        const uint32_t idesc = idesc_bf16_f32(TILE_M, CPAD);
-        const int hl_pad = T.n_hidden == 2 ? T.h2_pad : T.h1_pad;
-        const int ksteps = hl_pad / 16;
-        for (int k = 0; k < ksteps; ++k) {
-          const uint32_t a = hid_base + (uint32_t)(k >> 2) * HID_ATOM + (uint32_t)(k & 3) * 32u;
-          const uint32_t b = w3_base + (uint32_t)(k >> 2) * (CPAD * 128u) + (uint32_t)(k & 3) * 32u;
-          mma_bf16_ss(tmem_base + COL_ACC3, smem_desc_sw128(a), smem_desc_sw128(b), idesc, k > 0);
-        }
-        mma_commit(&bars->acc3_full);
-        mma_commit(&bars->w23_free);
-        pend = 0;
-      };
-      auto issue_pending = [&]() {
-        if (pend == 1) issue_layer2();
-        else if (pend == 2) issue_layer3();
-      };
-      int item = 0;
-      for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
-        for (int t = 0; t < w; ++t, ++item) {
-          const TrialDev& T = P.trial[t];
-          const int buf = item & 1;
-          const uint32_t idesc1 = idesc_bf16_f32(TILE_M, T.h1_pad);
-          const uint32_t d_tmem = tmem_base + COL_ACC1 + buf * HMAX;
-          mbar_wait(&bars->acc1_empty[buf], (uint32_t)(((item >> 1) & 1) ^ 1));
-          tc_fence_after_sync();
-          for (int kb = 0; kb < n_kb; ++kb) {
-            mbar_wait(&bars->full[stage], phase);
-            tc_fence_after_sync();
-            const int rem = (P.d - kb * KB) / 16;
-            const int ksteps = rem < 4 ? rem : 4;
-            const uint32_t a = a_base + (uint32_t)stage * A_STAGE;
-            const uint32_t b = b_base + (uint32_t)stage * B_STAGE;
-            for (int k = 0; k < ksteps; ++k)
-              mma_bf16_ss(d_tmem, smem_desc_sw128(a + k * 32), smem_desc_sw128(b + k * 32), idesc1, (kb | k) != 0);
-            mma_commit(&bars->empty[stage]);
-            if (kb == n_kb - 1) mma_commit(&bars->acc1_full[buf]);
-            if (++stage == STAGES) { stage = 0; phase ^= 1u; }
-            if (kb == KB_SLOT_A || kb == KB_SLOT_B) issue_pending();
-          }
-          while (pend != 0) issue_pending();        // short K loops: finish the previous item here
-          pend = T.n_hidden == 2 ? 1 : 2;
-          pend_item = item;
-          pend_t = t;
-        }
+    // =============================================================== MMA issuer
+    // Warp-uniform loop; one lane issues tcgen05.mma / tcgen05.commit.  Descriptors are a
+    // constant upper word plus (address >> 4) in the lower word, so stepping 16 K-elements
+    // (32 bytes) inside a swizzle atom is "+2" on a 32-bit register.
+    // Everything below is executed by all 32 lanes in lock step (mbarrier waits included); the
+    // *_elect helpers pick one lane per instruction, so there is no divergent region at all.
+    int stage = 0;
+    uint32_t phase = 0, hid_phase = 0;
+    const uint32_t a_lo0 = desc_lo_sw128(smem_base + OFF_A), b_lo0 = desc_lo_sw128(smem_base + OFF_B);
+    const uint32_t hid_lo = desc_lo_sw128(smem_base + OFF_HID);
+    const uint32_t w2_lo = desc_lo_sw128(smem_base + OFF_W2), w3_lo = desc_lo_sw128(smem_base + OFF_W3);
+    // layers 2/3 of a finished layer-1 item still to be issued: pend 1 = layer 2 next, 2 = layer 3 next
+    int pend = 0, pend_item = 0, pend_t = 0;
+    auto issue_small_layer = [&](uint32_t d_tmem, uint32_t b_lo, uint32_t b_atom, uint32_t idesc, int ksteps) {
+      // hidden tile (A) x small weight matrix (B); K runs over 64-wide atoms of 4 steps each
+      for (int k0 = 0; k0 < ksteps; k0 += 4) {
+        const uint32_t a = hid_lo + (uint32_t)(k0 >> 2) * (HID_ATOM >> 4);
+        const uint32_t b = b_lo + (uint32_t)(k0 >> 2) * b_atom;
+        mma4_f16_ss_elect(d_tmem, desc_from_lo(a), desc_from_lo(b), idesc, k0 != 0, ksteps - k0 < 4 ? ksteps - k0 : 4);
       }
-      while (pend != 0) issue_pending();
+    };
+    auto issue_layer2 = [&]() {
+      const TrialDev& T = P.trial[pend_t];
+      wait_prof<kProf>(&bars->w23_full, (uint32_t)(pend_item & 1), prof, PF_MMA_W23_FULL);
+      wait_prof<kProf>(&bars->hid_ready, hid_phase, prof, PF_MMA_HID_L2);
+      hid_phase ^= 1u;
+      tc_fence_after_sync();
+      issue_small_layer(tmem_base + COL_ACC2, w2_lo, ((uint32_t)T.h2_pad * 128u) >> 4,
+                        idesc_16bit_f32(kF16, TILE_M, T.h2_pad), T.h1_pad >> 4);
+      mma_commit_elect(&bars->acc2_full);
+      pend = 2;
+    };
+    auto issue_layer3 = [&]() {
+      const TrialDev& T = P.trial[pend_t];
+      if (T.n_hidden != 2) wait_prof<kProf>(&bars->w23_full, (uint32_t)(pend_item & 1), prof, PF_MMA_W23_FULL);
+      wait_prof<kProf>(&bars->hid_ready, hid_phase, prof, PF_MMA_HID_L3);
+      hid_phase ^= 1u;
+      tc_fence_after_sync();
+      const int hl_pad = T.n_hidden == 2 ? T.h2_pad : T.h1_pad;
+      issue_small_layer(tmem_base + COL_ACC3, w3_lo, (CPAD * 128u) >> 4, idesc_16bit_f32(kF16, TILE_M, CPAD),
+                        hl_pad >> 4);
+      mma_commit_elect(&bars->acc3_full);
+      mma_commit_elect(&bars->w23_free);
+      pend = 0;
+    };
+    auto issue_pending = [&]() {
+      if (pend == 1) issue_layer2();
+      else if (pend == 2) issue_layer3();
+    };
+    const int last_ksteps = (P.d - (n_kb - 1) * KB) >> 4;      // K steps of the ragged last block (1..4)
+    int item = 0;
+    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
+      for (int t = 0; t < w; ++t, ++item) {
+        const TrialDev& T = P.trial[t];
+        const int buf = item & 1;
+        const uint32_t idesc1 = idesc_16bit_f32(kF16, TILE_M, T.h1_pad);
+        const uint32_t d_tmem = tmem_base + COL_ACC1 + buf * HMAX;
+        wait_prof<kProf>(&bars->acc1_empty[buf], (uint32_t)(((item >> 1) & 1) ^ 1), prof, PF_MMA_ACC1_EMPTY);
+        tc_fence_after_sync();
+        for (int kb = 0; kb < n_kb; ++kb) {
+          wait_prof<kProf>(&bars->full[stage], phase, prof, PF_MMA_FULL);
+          tc_fence_after_sync();
+          const int ksteps = kb == n_kb - 1 ? last_ksteps : 4;
+          long long ti = 0;
+          if (kProf) ti = clock64();
+          if (!(P.debug & 4)) {
+            const uint32_t a = a_lo0 + (uint32_t)stage * (A_STAGE >> 4);
+            const uint32_t b = b_lo0 + (uint32_t)stage * (B_STAGE >> 4);
+            mma4_f16_ss_elect(d_tmem, desc_from_lo(a), desc_from_lo(b), idesc1, kb != 0, ksteps);
+          }
+          long long tc = 0;
+          if (kProf) {
+            tc = clock64();
+            prof[PF_MMA_ISSUE_L1] += tc - ti;
+          }
+          mma_commit_elect(&bars->empty[stage]);
+          if (kb == n_kb - 1) mma_commit_elect(&bars->acc1_full[buf]);
+          if (kProf) prof[PF_MMA_COMMIT_L1] += clock64() - tc;
+          if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+          if (kb == KB_SLOT_A || kb == KB_SLOT_B) issue_pending();
+        }
+        while (pend != 0) issue_pending();        // short K loops: finish the previous item here
+        pend = T.n_hidden == 2 ? 1 : 2;
+        pend_item = item;
+        pend_t = t;
+      }
     }
+    while (pend != 0) issue_pending();
+  }
+  if (kProf && P.prof != nullptr && lane == 0 &&
+      (warp == 0 || warp == kEpiWarps || warp == WARP_W1 || warp == WARP_MMA || warp == WARP_PAR)) {
+    const long long total = clock64() - t_start;
+    if (warp == 0) prof[PF_EPI_TOTAL] = total;
+    if (warp == kEpiWarps) prof[PF_PROD_TOTAL] = total;
+    if (warp == WARP_MMA) prof[PF_MMA_TOTAL] = total;
+    for (int i = 0; i < PF_COUNT; ++i)
+      if (prof[i] != 0) atomicAdd(reinterpret_cast<unsigned long long*>(P.prof + i), (unsigned long long)prof[i]);
   }
   __syncwarp();
   tc_fence_before_sync();
@@ -460,7 +587,7 @@ int upload_vec(T** dst, const std::vector<T>& v) {
 namespace rfk {
 
 bool fused_applicable(const rfk_mlp* h) {
-  if (h->dtype != RFK_BF16) return false;
+  if (h->dtype != RFK_BF16 && h->dtype != RFK_F16) return false;
   if (h->n_hidden < 1 || h->n_hidden > 2) return false;
   if (h->n_classes > CPAD || h->n_classes > RFK_MAX_CLASSES) return false;
   if (h->d % 16 != 0) return false;
@@ -475,19 +602,19 @@ int fused_prepare(rfk_mlp* h) {
   const Layer& l1 = h->layers[0];
   const Layer& l3 = h->layers[h->n_hidden];
   std::vector<uint8_t> img;
-  pack_kmajor_sw128(l1.w_bf16_host.data(), l1.out_pad, l1.in_pad, &img);
+  pack_kmajor_sw128(l1.w16_host.data(), l1.out_pad, l1.in_pad, &img);
   int rc = upload_vec(&s->w1, img);
   if (rc != RFK_OK) return rc;
   std::vector<float> bias(BIAS_FLOATS, 0.f);
   for (int j = 0; j < l1.out_pad; ++j) bias[j] = l1.b_fold_host[j];
   if (h->n_hidden == 2) {
     const Layer& l2 = h->layers[1];
-    pack_kmajor_sw128(l2.w_bf16_host.data(), l2.out_pad, l2.in_pad, &img);
+    pack_kmajor_sw128(l2.w16_host.data(), l2.out_pad, l2.in_pad, &img);
     rc = upload_vec(&s->w2, img);
     if (rc != RFK_OK) return rc;
     for (int j = 0; j < l2.out_pad; ++j) bias[HMAX + j] = l2.b_fold_host[j];
   }
-  pack_kmajor_sw128(l3.w_bf16_host.data(), l3.out_pad, l3.in_pad, &img);
+  pack_kmajor_sw128(l3.w16_host.data(), l3.out_pad, l3.in_pad, &img);
   rc = upload_vec(&s->w3, img);
   if (rc != RFK_OK) return rc;
   for (int j = 0; j < l3.out_pad && j < CPAD; ++j) bias[2 * HMAX + j] = l3.b_fold_host[j];
@@ -503,7 +630,12 @@ int fused_prepare(rfk_mlp* h) {
   s->dev.pad_ = 0;
   static bool attr_set[64] = {false};
   if (!attr_set[h->device & 63]) {
-    RFK_CUDA_TRY(cudaFuncSetAttribute(fused_ensemble_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    RFK_CUDA_TRY(cudaFuncSetAttribute(fused_ensemble_kernel<true, false>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    RFK_CUDA_TRY(cudaFuncSetAttribute(fused_ensemble_kernel<false, false>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    RFK_CUDA_TRY(cudaFuncSetAttribute(fused_ensemble_kernel<true, true>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
     attr_set[h->device & 63] = true;
   }
   return RFK_OK;
@@ -539,9 +671,38 @@ int fused_forward(rfk_mlp* const* trials, int w, int total_trials, const uint8_t
   P.total_trials = total_trials;
   P.n_classes = trials[0]->n_classes;
   P.n_tiles = (int)((n + TILE_M - 1) / TILE_M);
+  {
+    const char* dbg = getenv("RFK_FUSED_DEBUG");
+    P.debug = dbg ? atoi(dbg) : 0;
+  }
   const int sms = num_sms();
   const int grid = P.n_tiles < sms ? P.n_tiles : sms;
-  fused_ensemble_kernel<<<grid, kThreads, SMEM_BYTES, st>>>(P);
+  const char* prof_env = getenv("RFK_FUSED_PROF");
+  if (prof_env != nullptr && atoi(prof_env) != 0 && trials[0]->dtype == RFK_F16) {
+    // development aid: synchronous, allocates; prints the per-role blocked-cycle breakdown
+    long long* dprof = nullptr;
+    RFK_CUDA_TRY(cudaMalloc(&dprof, PF_COUNT * sizeof(long long)));
+    RFK_CUDA_TRY(cudaMemsetAsync(dprof, 0, PF_COUNT * sizeof(long long), st));
+    P.prof = dprof;
+    fused_ensemble_kernel<true, true><<<grid, kThreads, SMEM_BYTES, st>>>(P);
+    long long hprof[PF_COUNT];
+    RFK_CUDA_TRY(cudaMemcpyAsync(hprof, dprof, sizeof(hprof), cudaMemcpyDeviceToHost, st));
+    RFK_CUDA_TRY(cudaStreamSynchronize(st));
+    cudaFree(dprof);
+    static const char* names[PF_COUNT] = {"epi:bias_full", "epi:acc1_full", "epi:acc2_full", "epi:acc3_full",
+                                          "epi:TOTAL", "prod:empty", "prod:TOTAL", "w1:empty", "par:bias_free",
+                                          "par:w23_free", "mma:acc1_empty", "mma:full", "mma:w23_full",
+                                          "mma:hid_ready(L2)", "mma:hid_ready(L3)", "mma:TOTAL", "mma:issue(L1)",
+                                          "mma:commit(L1)", "mma:fence(L1)"};
+    const double items = (double)P.n_tiles * w;
+    fprintf(stderr, "[rfk prof] grid %d, items %g; cycles per item (avg over CTAs):\n", grid, items);
+    for (int i = 0; i < PF_COUNT; ++i) fprintf(stderr, "[rfk prof]   %-18s %10.0f\n", names[i], hprof[i] / items);
+    return RFK_OK;
+  }
+  if (trials[0]->dtype == RFK_F16)
+    fused_ensemble_kernel<true, false><<<grid, kThreads, SMEM_BYTES, st>>>(P);
+  else
+    fused_ensemble_kernel<false, false><<<grid, kThreads, SMEM_BYTES, st>>>(P);
   RFK_LAUNCH_CHECK("fused_ensemble_kernel");
   return RFK_OK;
 }

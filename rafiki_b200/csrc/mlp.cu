@@ -5,10 +5,10 @@
 // (Dense kernels [in, out], biases, BatchNormalization gamma/beta/moving mean/variance) and
 // keeps device copies in the layouts the kernels want.
 //
-// BatchNormalization folding (bf16 path).  With inv = gamma * rsqrt(var + eps),
+// BatchNormalization folding (tensor-core paths, 16-bit weights w' in bf16 or fp16).  With inv = gamma * rsqrt(var + eps),
 //   y_j = sum_i ((x_i - mean_i) * inv_i + beta_i) * K_ij + b_j
 //       = sum_i x_i * (inv_i * K_ij) + [b_j + sum_i beta_i * K_ij - sum_i mean_i * inv_i * K_ij].
-// The uint8 pixels x_i are exact in bf16, so the only rounding is w'_ij = bf16(inv_i * K_ij).
+// The uint8 pixels x_i are exact in bf16 and in fp16, so the only rounding is w'_ij = round16(inv_i * K_ij).
 // The constant uses the ROUNDED weights, c_j = b_j + sum_i beta_i K_ij - sum_i mean_i w'_ij,
 // which makes the error sum_i (x_i - mean_i) * (w'_ij - inv_i K_ij): it scales with the
 // centred pixel, exactly as rounding the normalised activation would, but with one rounding
@@ -37,8 +37,6 @@ void free_all(rfk_mlp* h) {
   for (rfk::Layer& l : h->layers) {
     cudaFree(l.w_f32);
     cudaFree(l.b_f32);
-    cudaFree(l.w_bf16);
-    cudaFree(l.b_fold);
   }
   delete h;
 }
@@ -56,8 +54,8 @@ extern "C" int rfk_mlp_create(rfk_mlp_t** out, int d, int n_hidden, const int* u
   RFK_REQUIRE(n_hidden == 0 || units != nullptr, "mlp_create: units is NULL");
   RFK_REQUIRE(kernels != nullptr && biases != nullptr, "mlp_create: kernels/biases is NULL");
   RFK_REQUIRE(bn_gamma && bn_beta && bn_mean && bn_var, "mlp_create: a BatchNormalization vector is NULL");
-  RFK_REQUIRE(compute_dtype == RFK_F32 || compute_dtype == RFK_BF16, "mlp_create: unknown compute_dtype %d",
-              compute_dtype);
+  RFK_REQUIRE(compute_dtype == RFK_F32 || compute_dtype == RFK_BF16 || compute_dtype == RFK_F16,
+              "mlp_create: unknown compute_dtype %d", compute_dtype);
   for (int i = 0; i < n_hidden; ++i) RFK_REQUIRE(units[i] >= 1, "mlp_create: units[%d]=%d", i, units[i]);
   for (int i = 0; i <= n_hidden; ++i)
     RFK_REQUIRE(kernels[i] != nullptr && biases[i] != nullptr, "mlp_create: layer %d tensors are NULL", i);
@@ -100,9 +98,9 @@ extern "C" int rfk_mlp_create(rfk_mlp_t** out, int d, int n_hidden, const int* u
       rc = upload(&l.w_f32, kernels[i], (size_t)l.in * l.out);
       if (rc == RFK_OK) rc = upload(&l.b_f32, biases[i], (size_t)l.out);
     } else {
-      std::vector<__nv_bfloat16> wt((size_t)l.out_pad * l.in_pad, __float2bfloat16(0.f));
+      std::vector<uint16_t> wt((size_t)l.out_pad * l.in_pad, 0);
       std::vector<float> bias(l.out_pad, 0.f);
-      for (int j = 0; j < l.out; ++j) {
+      for (int j = 0; j < l.out && rc == RFK_OK; ++j) {
         double c = (double)biases[i][j];
         for (int k = 0; k < l.in; ++k) {
           const double kij = (double)kernels[i][(size_t)k * l.out + j];
@@ -111,20 +109,32 @@ extern "C" int rfk_mlp_create(rfk_mlp_t** out, int d, int n_hidden, const int* u
             const double inv = (double)bn_gamma[k] / sqrt((double)bn_var[k] + (double)bn_eps);
             w = inv * kij;
           }
-          const __nv_bfloat16 wr = __float2bfloat16_rn((float)w);
-          wt[(size_t)j * l.in_pad + k] = wr;
-          if (i == 0) c += (double)bn_beta[k] * kij - (double)bn_mean[k] * (double)__bfloat162float(wr);
+          double wr;  // the weight as the tensor core will see it
+          if (compute_dtype == RFK_F16) {
+            if (!(fabs(w) <= 65504.0)) {
+              rfk::set_error("mlp_create: layer %d weight [%d,%d] = %g does not fit fp16; use RFK_BF16 or RFK_F32",
+                             i, k, j, w);
+              rc = RFK_ERR_UNSUPPORTED;
+              break;
+            }
+            const __half hv = __float2half_rn((float)w);
+            wt[(size_t)j * l.in_pad + k] = __half_as_ushort(hv);
+            wr = (double)__half2float(hv);
+          } else {
+            const __nv_bfloat16 bv = __float2bfloat16_rn((float)w);
+            wt[(size_t)j * l.in_pad + k] = __bfloat16_as_ushort(bv);
+            wr = (double)__bfloat162float(bv);
+          }
+          if (i == 0) c += (double)bn_beta[k] * kij - (double)bn_mean[k] * wr;
         }
         bias[j] = (float)c;
       }
-      rc = upload(&l.w_bf16, wt.data(), wt.size());
-      if (rc == RFK_OK) rc = upload(&l.b_fold, bias.data(), bias.size());
-      l.w_bf16_host.swap(wt);
+      l.w16_host.swap(wt);
       l.b_fold_host.swap(bias);
     }
     in = l.out;
   }
-  if (rc == RFK_OK && compute_dtype == RFK_BF16) {
+  if (rc == RFK_OK && compute_dtype != RFK_F32) {
     h->fusable = rfk::fused_applicable(h);
     rc = h->fusable ? rfk::fused_prepare(h) : rfk::tc_prepare(h);
   }
@@ -189,7 +199,7 @@ namespace {
 
 bool all_fusable(rfk_mlp_t* const* trials, int w) {
   for (int t = 0; t < w; ++t)
-    if (!(trials[t]->dtype == RFK_BF16 && trials[t]->fusable)) return false;
+    if (!(trials[t]->dtype == trials[0]->dtype && trials[t]->dtype != RFK_F32 && trials[t]->fusable)) return false;
   return true;
 }
 

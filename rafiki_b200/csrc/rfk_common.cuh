@@ -1,6 +1,7 @@
 // Shared host-side plumbing of librafiki_b200: error reporting and launch helpers.
 #pragma once
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -49,14 +50,12 @@ struct Layer {
   // fp32 path: Keras layout [in, out] row-major, bias [out]
   float* w_f32 = nullptr;
   float* b_f32 = nullptr;
-  // bf16 path: transposed and padded, [out_pad, in_pad] row-major ("K-major"), zero filled;
-  // layer 0 carries the folded BatchNormalization (see mlp.cu)
-  __nv_bfloat16* w_bf16 = nullptr;
-  float* b_fold = nullptr;  // [out_pad] bias (layer 0: bias + shift @ W with the rounded weights)
+  // tensor-core paths: 16-bit weights (bf16 or fp16 bit patterns, per rfk_mlp::dtype),
+  // transposed and padded to [out_pad, in_pad] row-major ("K-major"), zero filled; layer 0
+  // carries the folded BatchNormalization (see mlp.cu).  Host copies, consumed by the packers.
   int in_pad = 0, out_pad = 0;
-  // host copies of the two arrays above, kept for the packers of the tcgen05 paths
-  std::vector<__nv_bfloat16> w_bf16_host;
-  std::vector<float> b_fold_host;
+  std::vector<uint16_t> w16_host;
+  std::vector<float> b_fold_host;  // [out_pad] (layer 0: bias + shift @ W with the ROUNDED weights)
 };
 
 }  // namespace rfk

@@ -128,20 +128,74 @@ __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t smem_addr) {
   d |= (uint64_t)2 << 61;
   return d;
 }
-// Instruction descriptor for kind::f16 with bf16 A/B (both K-major), fp32 accumulate:
-// [4,6) D format 1 = f32; [7,10) A format 1 = bf16; [10,13) B format 1 = bf16;
+// The same descriptor split in two: the upper word is constant, the lower word carries the
+// address, so advancing inside a swizzle atom is a 32-bit add.
+__device__ __forceinline__ uint32_t desc_lo_sw128(uint32_t smem_addr) {
+  return ((smem_addr & 0x3FFFFu) >> 4) | (1u << 16);
+}
+__device__ __forceinline__ uint64_t desc_from_lo(uint32_t lo) {
+  constexpr uint32_t hi = (1024u >> 4) | (1u << 14) | (2u << 29);
+  return ((uint64_t)hi << 32) | (uint64_t)lo;
+}
+// Instruction descriptor for kind::f16 with fp16 or bf16 A/B (both K-major), fp32 accumulate:
+// [4,6) D format 1 = f32; [7,10) A format (0 = f16, 1 = bf16); [10,13) B format likewise;
 // bit 15/16 A/B major 0 = K; [17,23) N >> 3; [24,29) M >> 4.
-__host__ __device__ constexpr uint32_t idesc_bf16_f32(int m, int n) {
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+__host__ __device__ constexpr uint32_t idesc_16bit_f32(bool f16, int m, int n) {
+  return (1u << 4) | ((f16 ? 0u : 1u) << 7) | ((f16 ? 0u : 1u) << 10) | ((uint32_t)(n >> 3) << 17) |
+         ((uint32_t)(m >> 4) << 24);
 }
 // D[tmem] (+)= A[smem] * B[smem]^T, issued by ONE thread for the CTA.
-__device__ __forceinline__ void mma_bf16_ss(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+__device__ __forceinline__ void mma_f16_ss(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
                                             uint32_t accumulate) {
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
       "setp.ne.b32 p, %4, 0;\n\t"
       "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
       "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// Warp-converged variants: ALL 32 lanes execute the statement, elect.sync picks one lane and
+// the instruction itself is predicated on it.  The surrounding code stays convergent, so the
+// compiler keeps descriptors in uniform registers and emits no serialising loop per MMA.
+__device__ __forceinline__ void mma_f16_ss_elect(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                                  uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// Up to four K steps (16 elements = 32 bytes = +2 on the descriptor each) of one swizzle atom in
+// ONE statement: a single elect, one set of uniform operands, four predicated MMAs.  `nsteps`
+// is 1..4; the first step accumulates iff `accumulate_first`, the others always do.
+__device__ __forceinline__ void mma4_f16_ss_elect(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                                   uint32_t accumulate_first, int nsteps) {
+  asm volatile(
+      "{\n\t.reg .pred p, q, q2, q3, q4, t;\n\t"
+      ".reg .b64 a2, b2, a3, b3, a4, b4;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "setp.eq.u32 t, 0, 0;\n\t"
+      "setp.gt.and.s32 q2, %5, 1, q;\n\t"
+      "setp.gt.and.s32 q3, %5, 2, q;\n\t"
+      "setp.gt.and.s32 q4, %5, 3, q;\n\t"
+      "add.u64 a2, %1, 2;\n\tadd.u64 b2, %2, 2;\n\t"
+      "add.u64 a3, %1, 4;\n\tadd.u64 b3, %2, 4;\n\t"
+      "add.u64 a4, %1, 6;\n\tadd.u64 b4, %2, 6;\n\t"
+      "@q  tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "@q2 tcgen05.mma.cta_group::1.kind::f16 [%0], a2, b2, %3, t;\n\t"
+      "@q3 tcgen05.mma.cta_group::1.kind::f16 [%0], a3, b3, %3, t;\n\t"
+      "@q4 tcgen05.mma.cta_group::1.kind::f16 [%0], a4, b4, %3, t;\n\t}" ::"r"(d_tmem),
+      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate_first), "r"(nsteps)
+      : "memory");
+}
+__device__ __forceinline__ void mma_commit_elect(uint64_t* bar) {
+  asm volatile(
+      "{\n\t.reg .pred q;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
+      "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(smem_u32(bar))
       : "memory");
 }
 // Arrive on an mbarrier once every previously issued tcgen05.mma of this thread has

@@ -20,7 +20,9 @@ import torch
 
 from . import _native
 
-COMPUTE = {'f32': _native.RFK_F32, 'fp32': _native.RFK_F32, 'bf16': _native.RFK_BF16}
+COMPUTE = {'f32': _native.RFK_F32, 'fp32': _native.RFK_F32, 'bf16': _native.RFK_BF16,
+           'f16': _native.RFK_F16, 'fp16': _native.RFK_F16}
+DEFAULT_COMPUTE = 'f16'
 
 
 def _require_cuda():
@@ -63,7 +65,7 @@ class _Workspace:
 class Trial:
     """One packed trial (TfFeedForward network) on one GPU."""
 
-    def __init__(self, params, compute='bf16', device=None):
+    def __init__(self, params, compute=DEFAULT_COMPUTE, device=None):
         _require_cuda()
         self._lib = _native.load()
         self.device = torch.device('cuda', torch.cuda.current_device() if device is None else

@@ -41,19 +41,35 @@ def make_queries(n, image_size=28, channels=1, kind='uniform', seed=0, dead=None
         x = rng.integers(0, 256, size=shape, dtype=np.uint8)
     elif kind == 'fashion':
         x = np.zeros(shape, np.uint8)
-        r0 = rng.integers(0, image_size // 2, size=n)
-        c0 = rng.integers(0, image_size // 2, size=n)
-        hh = rng.integers(4, image_size // 2 + 1, size=n)
-        ww = rng.integers(4, image_size // 2 + 1, size=n)
+        # rectangles may hang over the border, so that every pixel is covered reasonably often
+        r0 = rng.integers(-(image_size // 2), image_size - 2, size=n)
+        c0 = rng.integers(-(image_size // 2), image_size - 2, size=n)
+        hh = rng.integers(image_size // 4, image_size + 1, size=n)
+        ww = rng.integers(image_size // 4, image_size + 1, size=n)
         for i in range(n):
-            blk = (hh[i], ww[i]) if channels == 1 else (hh[i], ww[i], channels)
-            v = np.clip(rng.normal(128.0, 48.0, size=blk), 0, 255).astype(np.uint8)
-            x[i, r0[i]:r0[i] + hh[i], c0[i]:c0[i] + ww[i]] = v
+            ra, rb = max(r0[i], 0), min(r0[i] + hh[i], image_size)
+            ca, cb = max(c0[i], 0), min(c0[i] + ww[i], image_size)
+            if rb <= ra or cb <= ca:
+                continue
+            blk = (rb - ra, cb - ca) if channels == 1 else (rb - ra, cb - ca, channels)
+            x[i, ra:rb, ca:cb] = np.clip(rng.normal(128.0, 48.0, size=blk), 0, 255).astype(np.uint8)
     else:
         raise ValueError('unknown query kind: {}'.format(kind))
     if dead is not None:
         x.reshape(n, d)[:, np.asarray(dead)] = 0
     return x
+
+
+_FASHION_STATS = {}
+
+
+def _fashion_stats(image_size, channels):
+    """Per-feature mean / variance of the 'fashion' query distribution (2048-image sample)."""
+    key = (image_size, channels)
+    if key not in _FASHION_STATS:
+        x = make_queries(2048, image_size, channels, 'fashion', seed=12345).reshape(2048, -1).astype(np.float64)
+        _FASHION_STATS[key] = (x.mean(0), x.var(0))
+    return _FASHION_STATS[key]
 
 
 def make_trial(t, image_size=28, channels=1, hidden_layer_count=None, hidden_layer_units=None,
@@ -72,12 +88,14 @@ def make_trial(t, image_size=28, channels=1, hidden_layer_count=None, hidden_lay
     if dead is None:
         dead = np.zeros(d, bool)
     dead = np.asarray(dead)
+    # moving statistics as training on this query distribution would leave them (+- jitter)
     if data_kind == 'uniform':
         mean = rng.normal(127.5, 6.0, size=d)
         var = rng.uniform(0.8, 1.2, size=d) * 5461.25
-    else:   # sparse "fashion" images: small means, wide spread of variances
-        mean = rng.uniform(0.0, 90.0, size=d)
-        var = rng.uniform(1.0, 80.0 ** 2, size=d)
+    else:
+        m0, v0 = _fashion_stats(image_size, channels)
+        mean = m0 * rng.uniform(0.95, 1.05, size=d)
+        var = v0 * rng.uniform(0.8, 1.2, size=d)
     mean[dead] = 0.0
     var[dead] = 0.0
     dims = [d] + [H] * L + [num_classes]

@@ -35,8 +35,7 @@ def _wire(p):
 @pytest.mark.parametrize('S', [28, 32])
 def test_dropin_model_file_through_the_plugin_harness(S, tmp_path, monkeypatch, golden_dir):
     monkeypatch.chdir(tmp_path)
-    dead = synth.dead_mask(S * S)
-    p = synth.make_trial(3, S, 1, 2, 36, dead=dead, data_kind='fashion')
+    p = synth.make_trial(3, S, 1, 2, 36, data_kind='fashion')
     queries = synth.make_queries(40, 28, 1, 'fashion', seed=2).tolist()     # 28x28 queries, resized when S = 32
     queries[0] = np.load(os.path.join(golden_dir, 'resize_reference.npz'))['sample_query'].tolist()
     model, preds = serve_model_class(MODEL_FILE, 'TfFeedForward', TaskType.IMAGE_CLASSIFICATION, _wire(p), queries,

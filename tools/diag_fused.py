@@ -48,7 +48,7 @@ def probe_trial(d, H, ks, L=1, s=1.0 / 64):
     return p
 
 
-def run(params, X, compute='bf16'):
+def run(params, X, compute='f16'):
     tr = engine.Trial(params, compute=compute)
     out = tr.forward(torch.from_numpy(X).cuda())
     torch.cuda.synchronize()
@@ -99,8 +99,11 @@ def main():
             return 1
         want = ff.forward(p, X[:8192], np.float32)
         err = np.abs(got[:8192] - want)
-        say('RAND S', S, 'ch', ch, 'L', L, 'H', H, 'n', n, 'maxerr %.3e' % err.max(),
-            'argmax agree %.5f' % np.mean(got[:8192].argmax(1) == want.argmax(1)))
+        gb = run(p, X, 'bf16')
+        say('RAND S', S, 'ch', ch, 'L', L, 'H', H, 'n', n, 'f16 maxerr %.3e' % err.max(),
+            'argmax agree %.5f' % np.mean(got[:8192].argmax(1) == want.argmax(1)),
+            '| bf16 maxerr %.3e' % np.abs(gb[:8192] - want).max(),
+            'argmax agree %.5f' % np.mean(gb[:8192].argmax(1) == want.argmax(1)))
     # 3. timing (device resident)
     dead = synth.dead_mask(784)
     for w, n in [(1, 65536), (3, 4096), (3, 65536), (8, 65536)]:

@@ -1,0 +1,31 @@
+"""Time the fused kernel (device resident) for a few (w, n); development tool."""
+import os, sys
+import torch
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from rafiki_b200 import engine, synth
+
+def main():
+    torch.cuda.set_device(0)
+    dead = synth.dead_mask(784)
+    cases = [(1, 65536), (8, 65536)] if len(sys.argv) < 2 else [tuple(int(v) for v in a.split('x')) for a in sys.argv[1:]]
+    for w, n in cases:
+        H = int(os.environ.get('RFK_H', '128'))
+        trials = [engine.Trial(synth.make_trial(t, 28, 1, 2, H, dead=dead)) for t in range(w)]
+        ens = engine.Ensemble(trials)
+        xs = [torch.from_numpy(synth.make_queries(n, 28, 1, 'uniform', seed=i, dead=dead)).cuda() for i in range(4)]
+        out = torch.empty((n, 10), dtype=torch.float32, device='cuda')
+        for i in range(3):
+            ens.forward(xs[i % 4], out=out)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        iters = 20
+        e0.record()
+        for i in range(iters):
+            ens.forward(xs[i % 4], out=out)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / iters
+        print('RFK_FUSED_DEBUG=%s w %d n %d: %.1f us/launch, %.0f Mq/s, %.0f TFLOP/s' % (
+            os.environ.get('RFK_FUSED_DEBUG', '0'), w, n, ms * 1e3, n / ms / 1e3, n * w * 236032 / ms / 1e9), flush=True)
+
+main()
