@@ -108,6 +108,19 @@ int rfk_mlp_forward(rfk_mlp_t* h, const uint8_t* x, int64_t n, float* probs, voi
                     size_t workspace_bytes, void* stream);
 
 /*
+ * The same forward pass for callers that cannot allocate.  (No counterpart in the reference;
+ * it serves hosts that run inside a memory budget fixed at start-up, or that receive raw
+ * device pointers from a framework whose allocator they may not call.)  RFK_F32 trials only.
+ * The intermediate activations go to a block of RFK_STATIC_SCRATCH_BYTES that is part of the
+ * library image on each GPU, so the call takes no workspace and calls no allocator.  A batch
+ * whose rfk_mlp_workspace_bytes exceeds that block is refused with RFK_ERR_INVALID.  The
+ * first call on a device resolves the block's address: make it before any stream capture.
+ * All calls on a GPU share the block: do not let two of them overlap in time.
+ */
+#define RFK_STATIC_SCRATCH_BYTES (4 * 1024 * 1024)
+int rfk_mlp_forward_static(rfk_mlp_t* h, const uint8_t* x, int64_t n, float* probs, void* stream);
+
+/*
  * Kernel 3 -- cross-trial probability averaging.
  * Replaces: ensemble_predictions, IMAGE_CLASSIFICATION branch
  * (rafiki/predictor/ensemble.py:10-14): out[i, :] = mean over trials of probs_w[i, :].

@@ -17,6 +17,7 @@ RFK_BF16 = 1
 RFK_F16 = 2
 RFK_MAX_TRIALS = 32
 RFK_MAX_CLASSES = 16
+RFK_STATIC_SCRATCH_BYTES = 4 * 1024 * 1024
 
 _ERR_NAMES = {1: 'RFK_ERR_INVALID', 2: 'RFK_ERR_CUDA', 3: 'RFK_ERR_UNSUPPORTED', 4: 'RFK_ERR_COMM'}
 
@@ -43,6 +44,7 @@ PROTOTYPES = {
     'rfk_mlp_info': (_i, [_vp, _c.POINTER(_i)]),
     'rfk_mlp_workspace_bytes': (_i, [_vp, _i64, _c.POINTER(_sz)]),
     'rfk_mlp_forward': (_i, [_vp, _vp, _i64, _vp, _vp, _sz, _vp]),
+    'rfk_mlp_forward_static': (_i, [_vp, _vp, _i64, _vp, _vp]),
     'rfk_ensemble_mean': (_i, [_c.POINTER(_vp), _i, _i64, _i, _vp, _vp]),
     'rfk_ensemble_workspace_bytes': (_i, [_c.POINTER(_vp), _i, _i64, _c.POINTER(_sz)]),
     'rfk_ensemble_forward': (_i, [_c.POINTER(_vp), _i, _i, _vp, _i64, _vp, _vp, _sz, _vp]),

@@ -5,7 +5,9 @@
 // round operands to bf16).  Layer 0 reads the uint8 queries directly and applies the
 // BatchNormalization affine while staging its A tile, so no decoded copy of the batch is
 // written.  The softmax is one warp-slice per row with shuffle reductions.
-#include "rfk_common.cuh"
+#include <mutex>
+
+#include "rfk_internal.cuh"
 
 namespace {
 
@@ -115,6 +117,10 @@ softmax_rows_kernel(const float* __restrict__ logits, float* __restrict__ probs,
 
 }  // namespace
 
+// Scratch of the allocation-free entry point rfk_mlp_forward_static (end of this file): a fixed
+// block of global memory that is part of the library image on every GPU that loads it.
+static __device__ __align__(256) unsigned char g_static_scratch[RFK_STATIC_SCRATCH_BYTES];
+
 namespace rfk {
 
 size_t mlp_f32_workspace_bytes(const rfk_mlp* h, int64_t n) {
@@ -162,3 +168,63 @@ int mlp_f32_forward(rfk_mlp* h, const uint8_t* x, int64_t n, float* probs, void*
 }
 
 }  // namespace rfk
+
+// ------------------------------------------------------------------------------------------
+// rfk_mlp_forward_static: the fp32 trial forward pass for callers that must not allocate.
+//
+// Some hosts of this library can hand over input and output buffers but cannot obtain scratch
+// memory at call time: a serving loop that runs inside a memory budget fixed at start-up, a
+// plugin that is given raw device pointers by a framework whose allocator it may not call, a
+// process that has handed the rest of the GPU to another tenant.  For them the intermediate
+// activations of the fp32 path live in g_static_scratch above instead of a caller workspace.
+//
+// What a caller should know:
+//  * The scratch is RFK_STATIC_SCRATCH_BYTES (4 MiB) of device memory per GPU, held from the
+//    moment the library is loaded on that GPU until the process exits.
+//  * A batch whose activations do not fit (two ping-pong buffers of n x widest-layer floats,
+//    the figure rfk_mlp_workspace_bytes reports) is refused with RFK_ERR_INVALID; split it.
+//  * The first call on each device looks up the device address of the scratch block
+//    (cudaGetSymbolAddress) with that device current, and remembers it.  Make that first call
+//    before starting any stream capture on the device.
+//  * Every call on a device uses the same block and leaves its activations behind in it.  Nothing
+//    in it has to start at zero: each element that a kernel reads was written earlier in the same
+//    call.  Two calls that overlap in time on one GPU (different streams, or different threads)
+//    would overwrite each other's activations; run them one after the other on one stream.
+//  * No cudaMalloc, cudaFree or other allocating routine is called, here or below.
+namespace {
+std::mutex g_static_mu;
+void* g_static_ptr[64] = {nullptr};   // device address of g_static_scratch, per device ordinal
+}  // namespace
+
+extern "C" int rfk_mlp_forward_static(rfk_mlp_t* h, const uint8_t* x, int64_t n, float* probs, void* stream) {
+  RFK_REQUIRE(h != nullptr, "mlp_forward_static: handle is NULL");
+  RFK_REQUIRE(h->dtype == RFK_F32, "mlp_forward_static: only RFK_F32 trials use scratch memory "
+              "(the tensor-core path of rfk_mlp_forward needs none and allocates nothing)");
+  RFK_REQUIRE(n >= 0, "mlp_forward_static: n=%lld", (long long)n);
+  if (n == 0) return RFK_OK;
+  RFK_REQUIRE(x != nullptr && probs != nullptr, "mlp_forward_static: NULL buffer");
+  int dev = 0;
+  RFK_CUDA_TRY(cudaGetDevice(&dev));
+  RFK_REQUIRE(dev == h->device, "mlp_forward_static: trial lives on device %d, current device is %d", h->device, dev);
+  RFK_REQUIRE(dev >= 0 && dev < 64, "mlp_forward_static: device ordinal %d not supported", dev);
+  const size_t need = rfk::mlp_f32_workspace_bytes(h, n);
+  if (need > (size_t)RFK_STATIC_SCRATCH_BYTES) {
+    rfk::set_error("mlp_forward_static: a batch of %lld queries needs %zu bytes of scratch, the built-in block "
+                   "holds %d; use a smaller batch or rfk_mlp_forward with your own workspace",
+                   (long long)n, need, RFK_STATIC_SCRATCH_BYTES);
+    return RFK_ERR_INVALID;
+  }
+  void* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    if (g_static_ptr[dev] == nullptr) {
+      // In host code the array's name is only a handle; the kernels need its device address.
+      void* p = nullptr;
+      RFK_CUDA_TRY(cudaGetSymbolAddress(&p, g_static_scratch));
+      g_static_ptr[dev] = p;
+    }
+    scratch = g_static_ptr[dev];
+  }
+  return rfk::mlp_f32_forward(h, x, n, probs, scratch, (size_t)RFK_STATIC_SCRATCH_BYTES,
+                              reinterpret_cast<cudaStream_t>(stream));
+}
