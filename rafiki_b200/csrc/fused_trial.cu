@@ -12,22 +12,27 @@
 // algorithmic minimum, d bytes in + 4*C bytes out per query, at which point the work
 // is bound by the tensor pipe (236 kflop per 824 bytes for D 784, H 128, L 2).
 //
-// Structure (one persistent CTA per SM, 480 threads, warp-specialised):
-//   warps 0-3  epilogue   TMEM -> registers, bias + ReLU -> bf16 hidden tile in shared memory
-//                         (the next layer's A operand); last layer: bias + softmax, and the
-//                         running ensemble sum in float64 registers; final store of the mean
-//   warps 4-11 A producer 16-byte loads of the uint8 tile (six pipeline steps of loads in
-//                         flight per thread, ~48 KB per SM, to cover HBM latency), exact
-//                         uint8 -> fp16/bf16 conversion, stores in the K-major 128B-swizzled
-//                         layout tcgen05.mma reads
-//   warp 12    W1 loader  cp.async.bulk (TMA engine) of the pre-swizzled first-layer weight
-//                         blocks into a 4-stage ring shared with the A producer
-//   warp 13    MMA issuer one thread issues every tcgen05.mma; accumulators live in TMEM
-//                         (2 x 128 columns for layer 1, double buffered so the epilogue of one
-//                         item overlaps the MMAs of the next, 128 for layer 2, 16 for layer 3)
-//   warp 14    parameter loader  cp.async.bulk of W2, W3 and the biases of the item's trial
+// Structure (one persistent CTA per SM, 640 threads in five warpgroups, warp-specialised; the
+// epilogue warpgroups take registers the light roles release, setmaxnreg):
+//   warps 0-7   epilogue   TMEM -> registers, bias + ReLU -> 16-bit hidden tile in shared memory
+//                          (the next layer's A operand).  Warps 0-3 own hidden columns 0-63,
+//                          warps 4-7 columns 64-127 (a warp may only touch the TMEM lanes
+//                          32*(warp%4)..+31, so two warps share each lane quarter).  Warps 0-3
+//                          also do the last layer: bias + softmax, the running ensemble sum in
+//                          float64 registers, and the final store of the mean.
+//   warps 8-15  converter  raw uint8 tile (shared memory) -> exact fp16/bf16 -> A operand tile
+//                          in the K-major 128B-swizzled layout tcgen05.mma reads
+//   warp 16     loader     per pipeline step one TMA tensor load of the 128 x 64-byte uint8
+//                          tile (out-of-range rows / columns arrive as zeros) into a 4-deep raw
+//                          ring, and one cp.async.bulk of the pre-swizzled first-layer weight
+//                          block into a 3-deep ring
+//   warp 17     MMA issuer convergent warp, one elected lane per tcgen05 statement; accumulators
+//                          live in TMEM (2 x 128 columns for layer 1, double buffered so the
+//                          epilogue of one item overlaps the MMAs of the next; 128 for layer 2;
+//                          16 for layer 3)
+//   warp 18     parameter loader  cp.async.bulk of W2, W3 and the biases of the item's trial
 // A work item is (tile of 128 queries, trial); items of one tile run back to back so the tile
-// stays hot in L1/L2 and the ensemble sum never leaves registers.
+// stays hot in L2 and the ensemble sum never leaves registers.
 //
 // BatchNormalization is folded into the first layer at pack time (mlp.cu), so the A operand
 // is the raw pixel value, which fp16 and bf16 both hold exactly.  Operands are fp16 (RFK_F16,
@@ -38,18 +43,21 @@
 #include "pack.cuh"
 #include "rfk_internal.cuh"
 #include "sm100.cuh"
+#include "tmap.cuh"
 
 namespace {
 
 using namespace sm100;
 
 constexpr int TILE_M = 128;
-constexpr int KB = 64;          // K elements per pipeline stage (one 128-byte swizzle atom of bf16)
-constexpr int STAGES = 4;
+constexpr int KB = 64;          // K elements per pipeline step (one 128-byte swizzle atom of 16-bit operands)
+constexpr int STAGES = 3;       // A / B operand ring
+constexpr int RAW_STAGES = 4;   // raw uint8 ring (TMA landing zone; covers HBM latency)
 constexpr int HMAX = 128;       // widest hidden layer the fused path takes
 constexpr int CPAD = 16;        // class dimension padded to one UMMA N step
 constexpr int A_STAGE = TILE_M * 128;
 constexpr int B_STAGE = HMAX * 128;
+constexpr int RAW_STAGE = TILE_M * KB;            // 8192 bytes of uint8
 constexpr int HID_ATOM = TILE_M * 128;
 constexpr int HID_BYTES = 2 * HID_ATOM;
 constexpr int W2_BYTES = 2 * HMAX * 128;
@@ -59,29 +67,34 @@ constexpr int BIAS_BYTES = BIAS_FLOATS * 4;
 
 constexpr int OFF_A = 0;
 constexpr int OFF_B = OFF_A + STAGES * A_STAGE;
-constexpr int OFF_HID = OFF_B + STAGES * B_STAGE;
+constexpr int OFF_RAW = OFF_B + STAGES * B_STAGE;
+constexpr int OFF_HID = OFF_RAW + RAW_STAGES * RAW_STAGE;
 constexpr int OFF_W2 = OFF_HID + HID_BYTES;
 constexpr int OFF_W3 = OFF_W2 + W2_BYTES;
 constexpr int OFF_BIAS = OFF_W3 + W3_BYTES;
 constexpr int OFF_BAR = OFF_BIAS + 2 * BIAS_BYTES;
-constexpr int NUM_BARS = 2 * STAGES + 13;
+constexpr int NUM_BARS = 2 * STAGES + 2 * RAW_STAGES + 13;
 constexpr int OFF_TMEM_SLOT = OFF_BAR + NUM_BARS * 8;
 constexpr int SMEM_USED = OFF_TMEM_SLOT + 16;
 constexpr int SMEM_BYTES = SMEM_USED + 1024;      // slack for the 1024-byte alignment of the base
+static_assert(OFF_HID % 1024 == 0 && OFF_W2 % 1024 == 0 && OFF_W3 % 1024 == 0 && OFF_B % 1024 == 0, "operand alignment");
+static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
 
-constexpr int kEpiWarps = 4, kProdWarps = 8;
-constexpr int kProdThreads = kProdWarps * 32;                 // 256: two 16-byte pieces per thread per step
-constexpr int kPrefetch = 6;                                  // pipeline steps of x loads in flight per thread
-constexpr int kThreads = (kEpiWarps + kProdWarps + 3) * 32;   // 480
-constexpr int WARP_W1 = kEpiWarps + kProdWarps, WARP_MMA = WARP_W1 + 1, WARP_PAR = WARP_W1 + 2;
+// Five warpgroups (setmaxnreg works per warpgroup): 0-1 epilogue, 2-3 converters, 4 = loader, MMA
+// issuer, parameter loader and one idle warp.  The kernel starts with 96 registers per thread;
+// the light roles give registers back and the epilogue warps take them.
+constexpr int kEpiWarps = 8, kConvWarps = 8;
+constexpr int kEpiThreads = kEpiWarps * 32;                   // 256
+constexpr int kConvThreads = kConvWarps * 32;                 // 256: two 16-byte pieces per thread per step
+constexpr int kConvPieces = (TILE_M * KB / 16) / kConvThreads;   // 2
+constexpr int kThreads = (kEpiWarps + kConvWarps + 4) * 32;   // 640
+constexpr int WARP_LOAD = kEpiWarps + kConvWarps, WARP_MMA = WARP_LOAD + 1, WARP_PAR = WARP_LOAD + 2;
+constexpr int kRegsEpi = 136, kRegsLight = 56;
 
 constexpr int TMEM_COLS = 512;
 constexpr int COL_ACC1 = 0;     // two buffers of 128 columns
 constexpr int COL_ACC2 = 256;
 constexpr int COL_ACC3 = 384;
-
-// when, during the layer-1 K loop of item i, the MMA thread slips in layers 2 and 3 of item i-1
-constexpr int KB_SLOT_A = 3, KB_SLOT_B = 8;
 
 struct TrialDev {
   const uint8_t* w1;    // [n_kb][h1_pad] rows of 128 B, swizzled
@@ -93,16 +106,17 @@ struct TrialDev {
 
 struct FusedParams {
   TrialDev trial[RFK_MAX_TRIALS];
-  const uint8_t* x;
   float* out;
   long long n;
   int d, n_kb, w, total_trials, n_classes, n_tiles;
   long long* prof;   // development only (RFK_FUSED_PROF): PF_COUNT counters, summed over CTAs
-  int debug;   // development only (RFK_FUSED_DEBUG): 1 skip W1 copies, 2 skip x loads/stores, 4 skip layer-1 MMAs
+  long long* trace;  // development only (RFK_FUSED_PROF=2): block 0 event timestamps, [4 roles][kTraceLen]
+  int debug;         // development only (RFK_FUSED_DEBUG): 1 skip W1 copies, 2 skip conversion, 4 skip layer-1 MMAs
 };
 
 struct Bars {
-  uint64_t full[STAGES], empty[STAGES];
+  uint64_t full[STAGES], empty[STAGES];           // A/B operand ring
+  uint64_t raw_full[RAW_STAGES], raw_empty[RAW_STAGES];
   uint64_t acc1_full[2], acc1_empty[2];
   uint64_t hid_ready, acc2_full, acc3_full, w23_full, w23_free;
   uint64_t bias_full[2], bias_free[2];
@@ -116,7 +130,6 @@ __device__ __forceinline__ uint32_t u8x2_to_bf16x2(uint32_t word, int e0) {
   const float f1 = __uint_as_float(__byte_perm(word, 0x4B000000u, 0x7440u | (e0 + 1))) - 8388608.0f;
   return __byte_perm(__float_as_uint(f0), __float_as_uint(f1), 0x7632u);
 }
-
 // exact uint8 -> fp16: 0x6400 | b is the half 1024 + b (ulp 1 in [1024, 2048)); subtract 1024.
 __device__ __forceinline__ uint32_t u8x2_to_f16x2(uint32_t word, int e0) {
   const uint32_t biased = __byte_perm(word, 0x64646464u, 0x4040u | (uint32_t)e0 | ((uint32_t)(e0 + 1) << 8));
@@ -129,75 +142,85 @@ __device__ __forceinline__ uint32_t u8x2_to_op(uint32_t word, int e0) {
   return kF16 ? u8x2_to_f16x2(word, e0) : u8x2_to_bf16x2(word, e0);
 }
 
-// two fp32 -> packed 16-bit operand pair (lo in the low half); fp16 saturates at +-65504
+// relu(lo), relu(hi) -> packed 16-bit operand pair (lo in the low half), one instruction;
+// fp16 saturates at 65504 instead of overflowing to infinity
 template <bool kF16>
-__device__ __forceinline__ uint32_t pack_op_x2(float lo, float hi) {
+__device__ __forceinline__ uint32_t relu_pack_x2(float lo, float hi) {
   uint32_t r;
-  if (kF16) {
-    lo = fminf(lo, 65504.f);
-    hi = fminf(hi, 65504.f);
-    asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
-  } else {
-    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
-  }
+  if (kF16)
+    asm("cvt.rn.relu.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  else
+    asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
   return r;
 }
 
-__device__ __forceinline__ uint4 ldg_u4(const uint8_t* p) {
+__device__ __forceinline__ uint4 lds_u4(uint32_t addr) {
   uint4 r;
-  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
-               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
-               : "l"(p));
+  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(addr));
   return r;
 }
-
 __device__ __forceinline__ void sts_u4(uint32_t addr, uint4 v) {
   asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
                : "memory");
 }
 
-// TMEM accumulator row -> bias + ReLU -> 16-bit -> hidden tile (A operand of the next layer).
-// Two 16-column TMEM loads are issued before the wait, 32 columns per iteration.
+// 16 accumulator columns of one row -> bias + ReLU -> 16-bit -> two 16-byte chunks of the hidden tile
 template <bool kF16>
-__device__ __forceinline__ void epilogue_hidden(uint32_t tmem_row_addr, int width, const float* bias,
+__device__ __forceinline__ void hidden_store16(const uint32_t (&v)[16], int c, const float* bias, uint32_t hid_base,
+                                               uint32_t row_off, uint32_t sw) {
+  const float4* b4 = reinterpret_cast<const float4*>(bias + c);
+  uint32_t p[8];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const float4 bb = b4[j];
+    p[2 * j] = relu_pack_x2<kF16>(__uint_as_float(v[4 * j + 0]) + bb.x, __uint_as_float(v[4 * j + 1]) + bb.y);
+    p[2 * j + 1] = relu_pack_x2<kF16>(__uint_as_float(v[4 * j + 2]) + bb.z, __uint_as_float(v[4 * j + 3]) + bb.w);
+  }
+  const uint32_t atom = hid_base + (uint32_t)(c >> 6) * HID_ATOM + row_off;
+  const uint32_t ch = (uint32_t)((c & 63) >> 3);
+  sts_u4(atom + (((ch) ^ sw) << 4), make_uint4(p[0], p[1], p[2], p[3]));
+  sts_u4(atom + (((ch + 1) ^ sw) << 4), make_uint4(p[4], p[5], p[6], p[7]));
+}
+
+// Columns [c_begin, c_end) of one TMEM accumulator row -> hidden tile (A operand of the next
+// layer).  16 columns per step; the TMEM load of step s+1 is in flight while step s is converted
+// and stored (two statically named buffers, so everything stays in registers).
+template <bool kF16>
+__device__ __forceinline__ void epilogue_hidden(uint32_t tmem_row_addr, int c_begin, int c_end, const float* bias,
                                                 uint32_t hid_base, int row) {
+  if (c_begin >= c_end) return;
   const uint32_t row_off = (uint32_t)row * 128u;
   const uint32_t sw = (uint32_t)(row & 7);
-  for (int c0 = 0; c0 < width; c0 += 32) {
-    uint32_t v[2][16];
-    const bool two = c0 + 16 < width;
-    tmem_ld16(tmem_row_addr + (uint32_t)c0, v[0]);
-    if (two) tmem_ld16(tmem_row_addr + (uint32_t)c0 + 16u, v[1]);
+  uint32_t va[16], vb[16];
+  tmem_ld16(tmem_row_addr + (uint32_t)c_begin, va);
+  for (int c = c_begin; c < c_end; c += 32) {
     tmem_ld_wait();
-#pragma unroll
-    for (int half = 0; half < 2; ++half) {
-      if (half == 1 && !two) break;
-      const int c = c0 + 16 * half;
-      const float4* b4 = reinterpret_cast<const float4*>(bias + c);
-      uint32_t p[8];
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const float4 bb = b4[j];
-        const float a0 = fmaxf(__uint_as_float(v[half][4 * j + 0]) + bb.x, 0.f);
-        const float a1 = fmaxf(__uint_as_float(v[half][4 * j + 1]) + bb.y, 0.f);
-        const float a2 = fmaxf(__uint_as_float(v[half][4 * j + 2]) + bb.z, 0.f);
-        const float a3 = fmaxf(__uint_as_float(v[half][4 * j + 3]) + bb.w, 0.f);
-        p[2 * j] = pack_op_x2<kF16>(a0, a1);
-        p[2 * j + 1] = pack_op_x2<kF16>(a2, a3);
-      }
-      const uint32_t atom = hid_base + (uint32_t)(c >> 6) * HID_ATOM + row_off;
-      const uint32_t ch = (uint32_t)((c & 63) >> 3);
-      sts_u4(atom + (((ch) ^ sw) << 4), make_uint4(p[0], p[1], p[2], p[3]));
-      sts_u4(atom + (((ch + 1) ^ sw) << 4), make_uint4(p[4], p[5], p[6], p[7]));
+    const bool more_b = c + 16 < c_end;
+    if (more_b) tmem_ld16(tmem_row_addr + (uint32_t)c + 16u, vb);
+    hidden_store16<kF16>(va, c, bias, hid_base, row_off, sw);
+    if (more_b) {
+      tmem_ld_wait();
+      if (c + 32 < c_end) tmem_ld16(tmem_row_addr + (uint32_t)c + 32u, va);
+      hidden_store16<kF16>(vb, c + 16, bias, hid_base, row_off, sw);
     }
   }
 }
 
 // kProf (development, RFK_FUSED_PROF=1): the leader thread of each warp role accumulates the
 // cycles it spends blocked on each kind of barrier and adds them to P.prof at exit.
-enum ProfSlot { PF_EPI_BIAS, PF_EPI_ACC1, PF_EPI_ACC2, PF_EPI_ACC3, PF_EPI_TOTAL, PF_PROD_EMPTY, PF_PROD_TOTAL,
-                PF_W1_EMPTY, PF_PAR_BIAS_FREE, PF_PAR_W23_FREE, PF_MMA_ACC1_EMPTY, PF_MMA_FULL, PF_MMA_W23_FULL,
-                PF_MMA_HID_L2, PF_MMA_HID_L3, PF_MMA_TOTAL, PF_MMA_ISSUE_L1, PF_MMA_COMMIT_L1, PF_MMA_FENCE, PF_COUNT };
+enum ProfSlot { PF_EPI_BIAS, PF_EPI_ACC1, PF_EPI_ACC2, PF_EPI_ACC3, PF_EPI_TOTAL, PF_CONV_RAW, PF_CONV_EMPTY,
+                PF_CONV_TOTAL, PF_LOAD_EMPTY, PF_LOAD_RAW_EMPTY, PF_PAR_BIAS_FREE, PF_PAR_W23_FREE, PF_MMA_ACC1_EMPTY,
+                PF_MMA_FULL, PF_MMA_W23_FULL, PF_MMA_HID_L2, PF_MMA_HID_L3, PF_MMA_TOTAL, PF_COUNT };
+
+constexpr int kTraceLen = 2048;
+// append a timestamp to a role's trace (block 0, leader lane only)
+#define RFK_TRACE(role, tag)                                                                      \
+  do {                                                                                           \
+    if (kProf && P.trace != nullptr && blockIdx.x == 0 && lane == 0 && trace_n < kTraceLen) {      \
+      P.trace[(role) * kTraceLen + trace_n] = (clock64() << 4) | (long long)(tag);                \
+      ++trace_n;                                                                                 \
+    }                                                                                            \
+  } while (0)
 
 template <bool kProf>
 __device__ __forceinline__ void wait_prof(uint64_t* bar, uint32_t parity, long long (&prof)[PF_COUNT], int slot) {
@@ -212,13 +235,14 @@ __device__ __forceinline__ void wait_prof(uint64_t* bar, uint32_t parity, long l
 
 template <bool kF16, bool kProf>
 __global__ void __launch_bounds__(kThreads, 1)
-fused_ensemble_kernel(const __grid_constant__ FusedParams P) {
+fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_constant__ CUtensorMap x_map) {
   long long prof[PF_COUNT];
   if (kProf) {
 #pragma unroll
     for (int i = 0; i < PF_COUNT; ++i) prof[i] = 0;
   }
   const long long t_start = kProf ? clock64() : 0;
+  int trace_n = 0;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   Bars* bars = reinterpret_cast<Bars*>(smem + OFF_BAR);
@@ -228,29 +252,33 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P) {
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < STAGES; ++s) {
-      mbar_init(&bars->full[s], kProdThreads + 1);
+      mbar_init(&bars->full[s], kConvThreads + 1);
       mbar_init(&bars->empty[s], 1);
+    }
+    for (int s = 0; s < RAW_STAGES; ++s) {
+      mbar_init(&bars->raw_full[s], 1);
+      mbar_init(&bars->raw_empty[s], kConvThreads);
     }
     for (int b = 0; b < 2; ++b) {
       mbar_init(&bars->acc1_full[b], 1);
-      mbar_init(&bars->acc1_empty[b], kEpiWarps * 32);
+      mbar_init(&bars->acc1_empty[b], kEpiThreads);
       mbar_init(&bars->bias_full[b], 1);
-      mbar_init(&bars->bias_free[b], kEpiWarps * 32);
+      mbar_init(&bars->bias_free[b], kEpiThreads);
     }
-    mbar_init(&bars->hid_ready, kEpiWarps * 32);
+    mbar_init(&bars->hid_ready, kEpiThreads);
     mbar_init(&bars->acc2_full, 1);
     mbar_init(&bars->acc3_full, 1);
     mbar_init(&bars->w23_full, 1);
     mbar_init(&bars->w23_free, 1);
     fence_mbar_init();
   }
+  if (warp == WARP_LOAD && lane == 0) tma_prefetch_desc(&x_map);
   if (warp == WARP_MMA) tmem_alloc<TMEM_COLS>(tmem_slot);
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
   // The kernel owns all 512 TMEM columns of its SM (one CTA per SM), so the allocation starts at
-  // column 0, lane 0.  Using the literal 0 keeps every TMEM address warp-uniform for the compiler
-  // (a value read back from shared memory is not, and costs a serialising loop around each MMA).
+  // column 0, lane 0.  Using the literal 0 keeps every TMEM address warp-uniform for the compiler.
   if (*tmem_slot != 0u) {
     if (threadIdx.x == 0) printf("rafiki_b200: unexpected TMEM base %u\n", *tmem_slot);
     __trap();
@@ -263,8 +291,11 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P) {
 
   if (warp < kEpiWarps) {
     // =============================================================== epilogue warps
-    const int row = threadIdx.x;                               // TMEM lane == row of the tile
-    const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kRegsEpi));
+    const int quarter = warp & 3;                              // TMEM lane quarter this warp may touch
+    const int half = warp >> 2;                                // 0: hidden columns 0-63 + softmax; 1: columns 64-127
+    const int row = quarter * 32 + lane;                       // TMEM lane == row of the tile
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(quarter * 32) << 16);
     const uint32_t hid_base = smem_base + OFF_HID;
     double acc[CPAD];
 #pragma unroll
@@ -281,139 +312,172 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P) {
         wait_prof<kProf>(&bars->bias_full[buf], par2, prof, PF_EPI_BIAS);
         // ---- layer 1: acc1[buf] -> hidden
         wait_prof<kProf>(&bars->acc1_full[buf], par2, prof, PF_EPI_ACC1);
+        if (warp == 0) RFK_TRACE(3, 1);
         tc_fence_after_sync();
-        epilogue_hidden<kF16>(lane_addr + COL_ACC1 + buf * HMAX, T.h1_pad, bias, hid_base, row);
+        {
+          const int split = T.h1_pad < 64 ? T.h1_pad : 64;
+          epilogue_hidden<kF16>(lane_addr + COL_ACC1 + buf * HMAX, half ? split : 0, half ? T.h1_pad : split, bias,
+                                hid_base, row);
+        }
         tc_fence_before_sync();
         mbar_arrive(&bars->acc1_empty[buf]);
         fence_proxy_async_smem();
         mbar_arrive(&bars->hid_ready);
+        if (warp == 0) RFK_TRACE(3, 2);
         // ---- layer 2 (two-hidden-layer trials): acc2 -> hidden
         if (T.n_hidden == 2) {
           wait_prof<kProf>(&bars->acc2_full, acc2_phase, prof, PF_EPI_ACC2);
+          if (warp == 0) RFK_TRACE(3, 3);
           acc2_phase ^= 1u;
           tc_fence_after_sync();
-          epilogue_hidden<kF16>(lane_addr + COL_ACC2, T.h2_pad, bias + HMAX, hid_base, row);
+          const int split = T.h2_pad < 64 ? T.h2_pad : 64;
+          epilogue_hidden<kF16>(lane_addr + COL_ACC2, half ? split : 0, half ? T.h2_pad : split, bias + HMAX, hid_base,
+                                row);
           tc_fence_before_sync();
           fence_proxy_async_smem();
           mbar_arrive(&bars->hid_ready);
+          if (warp == 0) RFK_TRACE(3, 4);
         }
-        // ---- softmax layer: acc3 -> probabilities -> running ensemble sum
+        // ---- softmax layer: both halves wait (the hidden tile may not be overwritten before the
+        //      layer-3 MMAs have read it); half 0 turns acc3 into probabilities and sums them
         wait_prof<kProf>(&bars->acc3_full, par1, prof, PF_EPI_ACC3);
+        if (warp == 0) RFK_TRACE(3, 5);
         tc_fence_after_sync();
-        uint32_t v[16];
-        tmem_ld16(lane_addr + COL_ACC3, v);
-        tmem_ld_wait();
-        tc_fence_before_sync();
-        float z[CPAD];
-        float mx = -INFINITY;
+        if (half == 0) {
+          uint32_t v[16];
+          tmem_ld16(lane_addr + COL_ACC3, v);
+          tmem_ld_wait();
+          tc_fence_before_sync();
+          float z[CPAD];
+          float mx = -INFINITY;
 #pragma unroll
-        for (int j = 0; j < CPAD; ++j) {
-          z[j] = __uint_as_float(v[j]) + bias[2 * HMAX + j];
-          if (j < P.n_classes) mx = fmaxf(mx, z[j]);
+          for (int j = 0; j < CPAD; ++j) {
+            z[j] = __uint_as_float(v[j]) + bias[2 * HMAX + j];
+            if (j < P.n_classes) mx = fmaxf(mx, z[j]);
+          }
+          float sum = 0.f;
+#pragma unroll
+          for (int j = 0; j < CPAD; ++j) {
+            z[j] = j < P.n_classes ? __expf(z[j] - mx) : 0.f;
+            sum += z[j];
+          }
+          const float inv = 1.0f / sum;
+          mbar_arrive(&bars->bias_free[buf]);
+#pragma unroll
+          for (int j = 0; j < CPAD; ++j) acc[j] += (double)(z[j] * inv);
+          if (warp == 0) RFK_TRACE(3, 6);
+        } else {
+          mbar_arrive(&bars->bias_free[buf]);
         }
-        float sum = 0.f;
-#pragma unroll
-        for (int j = 0; j < CPAD; ++j) {
-          z[j] = j < P.n_classes ? expf(z[j] - mx) : 0.f;
-          sum += z[j];
-        }
-        mbar_arrive(&bars->bias_free[buf]);
-#pragma unroll
-        for (int j = 0; j < CPAD; ++j) acc[j] += (double)(z[j] / sum);
       }
       // ---- the tile's ensemble mean: float64 sum in trial order, one division, one rounding
-      const long long grow = (long long)tile * TILE_M + row;
-      if (grow < P.n) {
-        float* o = P.out + grow * P.n_classes;
+      if (half == 0) {
+        const long long grow = (long long)tile * TILE_M + row;
+        if (grow < P.n) {
+          float* o = P.out + grow * P.n_classes;
 #pragma unroll
-        for (int j = 0; j < CPAD; ++j)
-          if (j < P.n_classes) o[j] = (float)(acc[j] / (double)P.total_trials);
+          for (int j = 0; j < CPAD; ++j)
+            if (j < P.n_classes) o[j] = (float)(acc[j] / (double)P.total_trials);
+        }
+#pragma unroll
+        for (int j = 0; j < CPAD; ++j) acc[j] = 0.0;
       }
-#pragma unroll
-      for (int j = 0; j < CPAD; ++j) acc[j] = 0.0;
     }
-  } else if (warp < kEpiWarps + kProdWarps) {
-    // =============================================================== A producer warps
-    // A pipeline step is one 64-wide K block of one item: 128 rows x 64 bytes of uint8.  Each of
-    // the 256 threads owns two 16-byte pieces of it (rows r_in and r_in + 64, quarter q) and
-    // keeps kPrefetch steps of loads in flight in a register ring.
-    const int tp = threadIdx.x - kEpiWarps * 32;                 // 0..255
-    const int q = tp & 3;                                        // 16-byte quarter of the 64-byte row chunk
-    const int r_in = tp >> 2;                                    // 0..63
-    const uint32_t a_base = smem_base + OFF_A;
-    const int d = P.d;
-    int my_tiles = 0;
-    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) ++my_tiles;
-    const int total_steps = my_tiles * w * n_kb;
-    uint4 ring[kPrefetch][2];
-    // load cursor
-    int l_tile = blockIdx.x, l_t = 0, l_kb = 0, l_step = 0;
-    auto load_next = [&](uint4 (&dst)[2]) {
-      if (l_step < total_steps) {
-        const long long row0 = (long long)l_tile * TILE_M;
-        const int k = l_kb * KB + q * 16;
+  } else if (warp < kEpiWarps + kConvWarps) {
+    // =============================================================== converter warps
+    // One step = one 64-wide K block of one item: 128 rows x 64 bytes of uint8 in the raw ring.
+    // Thread tp owns the 16-byte pieces (row = it*64 + tp/4, quarter = tp%4), it = 0..1; all
+    // offsets are fixed per thread, so a step is 2 x (LDS.128, 16 conversions, 2 x STS.128).
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsLight));
+    const int tp = threadIdx.x - kEpiThreads;                    // 0..255
+    const int q = tp & 3;
+    const int r0 = tp >> 2;                                      // 0..63
+    const uint32_t sw = (uint32_t)(r0 & 7);
+    const uint32_t raw_off = smem_base + OFF_RAW + (uint32_t)r0 * KB + (uint32_t)q * 16u;
+    const uint32_t a_off_lo = smem_base + OFF_A + (uint32_t)r0 * 128u + ((((uint32_t)(2 * q)) ^ sw) << 4);
+    const uint32_t a_off_hi = smem_base + OFF_A + (uint32_t)r0 * 128u + ((((uint32_t)(2 * q + 1)) ^ sw) << 4);
+    const int last_cols = P.d - (n_kb - 1) * KB;                 // valid bytes per row in the ragged last block
+    constexpr uint32_t kRowsPerPass = TILE_M / kConvPieces;      // 64
+    int stage = 0, rstage = 0;
+    uint32_t phase = 0, rphase = 0;
+    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
+      for (int t = 0; t < w; ++t) {
+        for (int kb = 0; kb < n_kb; ++kb) {
+          wait_prof<kProf>(&bars->raw_full[rstage], rphase, prof, PF_CONV_RAW);
+          if (warp == kEpiWarps) RFK_TRACE(0, 1);
+          wait_prof<kProf>(&bars->empty[stage], phase ^ 1u, prof, PF_CONV_EMPTY);
+          if (warp == kEpiWarps) RFK_TRACE(0, 2);
+          // columns past the end of the row are never read by the MMAs: skip their conversion
+          const bool live = !(P.debug & 2) && (kb < n_kb - 1 || q * 16 < last_cols);
+          if (live) {
+            const uint32_t rsrc = raw_off + (uint32_t)rstage * RAW_STAGE;
+            const uint32_t dlo = a_off_lo + (uint32_t)stage * A_STAGE;
+            const uint32_t dhi = a_off_hi + (uint32_t)stage * A_STAGE;
+            uint4 raw[kConvPieces];
 #pragma unroll
-        for (int it = 0; it < 2; ++it) {
-          const long long grow = row0 + it * 64 + r_in;
-          dst[it] = (grow < P.n && k < d && !(P.debug & 2)) ? ldg_u4(P.x + grow * d + k) : make_uint4(0u, 0u, 0u, 0u);
-        }
-        ++l_step;
-        if (++l_kb == n_kb) {
-          l_kb = 0;
-          if (++l_t == w) {
-            l_t = 0;
-            l_tile += gridDim.x;
-          }
-        }
-      }
-    };
+            for (int it = 0; it < kConvPieces; ++it) raw[it] = lds_u4(rsrc + (uint32_t)it * (kRowsPerPass * KB));
 #pragma unroll
-    for (int j = 0; j < kPrefetch; ++j) load_next(ring[j]);
-    int stage = 0;
-    uint32_t phase = 0;
-    for (int s0 = 0; s0 < total_steps; s0 += kPrefetch) {
-#pragma unroll
-      for (int j = 0; j < kPrefetch; ++j) {
-        if (s0 + j < total_steps) {
-          wait_prof<kProf>(&bars->empty[stage], phase ^ 1u, prof, PF_PROD_EMPTY);
-          const uint32_t st_base = a_base + (uint32_t)stage * A_STAGE;
-#pragma unroll
-          for (int it = 0; it < 2; ++it) {
-            if (P.debug & 2) break;
-            const int row = it * 64 + r_in;
-            const uint4 raw = ring[j][it];
-            const uint4 lo = make_uint4(u8x2_to_op<kF16>(raw.x, 0), u8x2_to_op<kF16>(raw.x, 2),
-                                        u8x2_to_op<kF16>(raw.y, 0), u8x2_to_op<kF16>(raw.y, 2));
-            const uint4 hi = make_uint4(u8x2_to_op<kF16>(raw.z, 0), u8x2_to_op<kF16>(raw.z, 2),
-                                        u8x2_to_op<kF16>(raw.w, 0), u8x2_to_op<kF16>(raw.w, 2));
-            const uint32_t rbase = st_base + (uint32_t)row * 128u;
-            const uint32_t sw = (uint32_t)(row & 7);
-            sts_u4(rbase + ((((uint32_t)(2 * q)) ^ sw) << 4), lo);
-            sts_u4(rbase + ((((uint32_t)(2 * q + 1)) ^ sw) << 4), hi);
+            for (int it = 0; it < kConvPieces; ++it) {
+              const uint4 lo = make_uint4(u8x2_to_op<kF16>(raw[it].x, 0), u8x2_to_op<kF16>(raw[it].x, 2),
+                                          u8x2_to_op<kF16>(raw[it].y, 0), u8x2_to_op<kF16>(raw[it].y, 2));
+              const uint4 hi = make_uint4(u8x2_to_op<kF16>(raw[it].z, 0), u8x2_to_op<kF16>(raw[it].z, 2),
+                                          u8x2_to_op<kF16>(raw[it].w, 0), u8x2_to_op<kF16>(raw[it].w, 2));
+              sts_u4(dlo + (uint32_t)it * (kRowsPerPass * 128u), lo);
+              sts_u4(dhi + (uint32_t)it * (kRowsPerPass * 128u), hi);
+            }
           }
           fence_proxy_async_smem();
           mbar_arrive(&bars->full[stage]);
-          load_next(ring[j]);
+          mbar_arrive(&bars->raw_empty[rstage]);
+          if (warp == kEpiWarps) RFK_TRACE(0, 3);
           if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+          if (++rstage == RAW_STAGES) { rstage = 0; rphase ^= 1u; }
         }
       }
     }
-  } else if (warp == WARP_W1) {
-    // =============================================================== first-layer weight loader
-    // The whole warp runs the loop (warp-uniform control flow keeps addresses in uniform
-    // registers); lane 0 alone issues the copies.
-    int stage = 0;
-    uint32_t phase = 0;
-#ifdef RFK_LOADER_SINGLE
-    if (lane == 0)
-#endif
+  } else {
+    // warpgroup 4: loader, MMA issuer, parameter loader, idle warp -- all give registers back
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsLight));
+  }
+  if (warp == WARP_LOAD) {
+    // =============================================================== loader: raw query tiles + first-layer weights
+    // The raw ring runs ahead of the operand ring: the TMA load of step s + RAW_STAGES - 1 is in
+    // flight while step s is being converted.
+    int stage = 0, rstage = 0;
+    uint32_t phase = 0, rphase = 0;
+    int my_tiles = 0;
+    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) ++my_tiles;
+    const int total_steps = my_tiles * w * n_kb;
+    // raw cursor (runs ahead)
+    int r_tile = blockIdx.x, r_t = 0, r_kb = 0, r_step = 0;
+    auto issue_raw = [&]() {
+      wait_prof<kProf>(&bars->raw_empty[rstage], rphase ^ 1u, prof, PF_LOAD_RAW_EMPTY);
+      RFK_TRACE(1, 1);
+      if (lane == 0) {
+        mbar_arrive_expect_tx(&bars->raw_full[rstage], RAW_STAGE);
+        tma_load_2d(smem + OFF_RAW + rstage * RAW_STAGE, &x_map, r_kb * KB, r_tile * TILE_M, &bars->raw_full[rstage]);
+      }
+      __syncwarp();
+      if (++rstage == RAW_STAGES) { rstage = 0; rphase ^= 1u; }
+      ++r_step;
+      if (++r_kb == n_kb) {
+        r_kb = 0;
+        if (++r_t == w) {
+          r_t = 0;
+          r_tile += gridDim.x;
+        }
+      }
+    };
+    for (int i = 0; i < RAW_STAGES - 1 && r_step < total_steps; ++i) issue_raw();
     for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
       for (int t = 0; t < w; ++t) {
         const TrialDev& T = P.trial[t];
         const uint32_t bytes = (uint32_t)T.h1_pad * 128u;
         const uint8_t* src = T.w1;
         for (int kb = 0; kb < n_kb; ++kb) {
-          wait_prof<kProf>(&bars->empty[stage], phase ^ 1u, prof, PF_W1_EMPTY);
+          if (r_step < total_steps) issue_raw();
+          wait_prof<kProf>(&bars->empty[stage], phase ^ 1u, prof, PF_LOAD_EMPTY);
+          RFK_TRACE(1, 3);
           if (lane == 0) {
             if (P.debug & 1) {
               mbar_arrive(&bars->full[stage]);
@@ -422,9 +486,7 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P) {
               bulk_g2s(smem + OFF_B + stage * B_STAGE, src + (size_t)kb * bytes, bytes, &bars->full[stage]);
             }
           }
-#ifndef RFK_LOADER_SINGLE
           __syncwarp();
-#endif
           if (++stage == STAGES) { stage = 0; phase ^= 1u; }
         }
       }
@@ -432,9 +494,6 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P) {
   } else if (warp == WARP_PAR) {
     // =============================================================== per-trial parameter loader
     int item = 0;
-#ifdef RFK_LOADER_SINGLE
-    if (lane == 0)
-#endif
     for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
       for (int t = 0; t < w; ++t, ++item) {
         const TrialDev& T = P.trial[t];
@@ -444,9 +503,7 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P) {
           mbar_arrive_expect_tx(&bars->bias_full[buf], BIAS_BYTES);
           bulk_g2s(smem + OFF_BIAS + buf * BIAS_BYTES, T.bias, BIAS_BYTES, &bars->bias_full[buf]);
         }
-#ifndef RFK_LOADER_SINGLE
         __syncwarp();
-#endif
         wait_prof<kProf>(&bars->w23_free, (uint32_t)((item & 1) ^ 1), prof, PF_PAR_W23_FREE);
         const int hl_pad = T.n_hidden == 2 ? T.h2_pad : T.h1_pad;
         const uint32_t w3_bytes = (uint32_t)((hl_pad + 63) / 64) * CPAD * 128u;
@@ -456,18 +513,14 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P) {
           if (w2_bytes) bulk_g2s(smem + OFF_W2, T.w2, w2_bytes, &bars->w23_full);
           bulk_g2s(smem + OFF_W3, T.w3, w3_bytes, &bars->w23_full);
         }
-#ifndef RFK_LOADER_SINGLE
         __syncwarp();
-#endif
       }
     }
   } else if (warp == WARP_MMA) {
     // =============================================================== MMA issuer
-    // Warp-uniform loop; one lane issues tcgen05.mma / tcgen05.commit.  Descriptors are a
-    // constant upper word plus (address >> 4) in the lower word, so stepping 16 K-elements
-    // (32 bytes) inside a swizzle atom is "+2" on a 32-bit register.
     // Everything below is executed by all 32 lanes in lock step (mbarrier waits included); the
-    // *_elect helpers pick one lane per instruction, so there is no divergent region at all.
+    // *_elect helpers pick one lane per statement, so there is no divergent region at all.
+    // Descriptors are a constant upper word plus (address >> 4) in the lower word.
     int stage = 0;
     uint32_t phase = 0, hid_phase = 0;
     const uint32_t a_lo0 = desc_lo_sw128(smem_base + OFF_A), b_lo0 = desc_lo_sw128(smem_base + OFF_B);
@@ -507,9 +560,14 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P) {
       mma_commit_elect(&bars->w23_free);
       pend = 0;
     };
-    auto issue_pending = [&]() {
-      if (pend == 1) issue_layer2();
-      else if (pend == 2) issue_layer3();
+    // Layers 2/3 of the previous item are slipped into this item's layer-1 K loop as soon as the
+    // epilogue has published their input (non-blocking probe); whatever is left is finished,
+    // blocking, after the loop.
+    auto poll_pending = [&]() {
+      if (pend != 0 && mbar_test(&bars->hid_ready, hid_phase)) {
+        if (pend == 1) issue_layer2();
+        else issue_layer3();
+      }
     };
     const int last_ksteps = (P.d - (n_kb - 1) * KB) >> 4;      // K steps of the ragged last block (1..4)
     int item = 0;
@@ -523,39 +581,41 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P) {
         tc_fence_after_sync();
         for (int kb = 0; kb < n_kb; ++kb) {
           wait_prof<kProf>(&bars->full[stage], phase, prof, PF_MMA_FULL);
+          RFK_TRACE(2, 1);
           tc_fence_after_sync();
           const int ksteps = kb == n_kb - 1 ? last_ksteps : 4;
-          long long ti = 0;
-          if (kProf) ti = clock64();
           if (!(P.debug & 4)) {
             const uint32_t a = a_lo0 + (uint32_t)stage * (A_STAGE >> 4);
             const uint32_t b = b_lo0 + (uint32_t)stage * (B_STAGE >> 4);
             mma4_f16_ss_elect(d_tmem, desc_from_lo(a), desc_from_lo(b), idesc1, kb != 0, ksteps);
           }
-          long long tc = 0;
-          if (kProf) {
-            tc = clock64();
-            prof[PF_MMA_ISSUE_L1] += tc - ti;
-          }
+          RFK_TRACE(2, 2);
           mma_commit_elect(&bars->empty[stage]);
           if (kb == n_kb - 1) mma_commit_elect(&bars->acc1_full[buf]);
-          if (kProf) prof[PF_MMA_COMMIT_L1] += clock64() - tc;
+          RFK_TRACE(2, 3);
           if (++stage == STAGES) { stage = 0; phase ^= 1u; }
-          if (kb == KB_SLOT_A || kb == KB_SLOT_B) issue_pending();
+          poll_pending();
+          RFK_TRACE(2, 4);
         }
-        while (pend != 0) issue_pending();        // short K loops: finish the previous item here
+        while (pend != 0) {                          // finish the previous item before queueing this one's tail
+          if (pend == 1) issue_layer2();
+          else issue_layer3();
+        }
         pend = T.n_hidden == 2 ? 1 : 2;
         pend_item = item;
         pend_t = t;
       }
     }
-    while (pend != 0) issue_pending();
+    while (pend != 0) {
+      if (pend == 1) issue_layer2();
+      else issue_layer3();
+    }
   }
   if (kProf && P.prof != nullptr && lane == 0 &&
-      (warp == 0 || warp == kEpiWarps || warp == WARP_W1 || warp == WARP_MMA || warp == WARP_PAR)) {
+      (warp == 0 || warp == kEpiWarps || warp == WARP_LOAD || warp == WARP_MMA || warp == WARP_PAR)) {
     const long long total = clock64() - t_start;
     if (warp == 0) prof[PF_EPI_TOTAL] = total;
-    if (warp == kEpiWarps) prof[PF_PROD_TOTAL] = total;
+    if (warp == kEpiWarps) prof[PF_CONV_TOTAL] = total;
     if (warp == WARP_MMA) prof[PF_MMA_TOTAL] = total;
     for (int i = 0; i < PF_COUNT; ++i)
       if (prof[i] != 0) atomicAdd(reinterpret_cast<unsigned long long*>(P.prof + i), (unsigned long long)prof[i]);
@@ -655,6 +715,13 @@ void fused_release(rfk_mlp* h) {
 int fused_forward(rfk_mlp* const* trials, int w, int total_trials, const uint8_t* x, int64_t n, float* out,
                   cudaStream_t st) {
   RFK_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0, "fused forward: x must be 16-byte aligned");
+  const int d = trials[0]->d;
+  // TMA descriptor of the query batch: uint8 [n, d]; one box = 128 rows x 64 bytes
+  CUtensorMap x_map;
+  {
+    const int rc = make_tmap_u8_2d(&x_map, x, (uint64_t)n, (uint64_t)d, (uint64_t)d, TILE_M, KB);
+    if (rc != RFK_OK) return rc;
+  }
   FusedParams P;
   memset(&P, 0, sizeof(P));
   for (int t = 0; t < w; ++t) {
@@ -662,7 +729,6 @@ int fused_forward(rfk_mlp* const* trials, int w, int total_trials, const uint8_t
     RFK_REQUIRE(s != nullptr, "fused forward: trial %d was not packed for the fused path", t);
     P.trial[t] = s->dev;
   }
-  P.x = x;
   P.out = out;
   P.n = n;
   P.d = trials[0]->d;
@@ -681,28 +747,44 @@ int fused_forward(rfk_mlp* const* trials, int w, int total_trials, const uint8_t
   if (prof_env != nullptr && atoi(prof_env) != 0 && trials[0]->dtype == RFK_F16) {
     // development aid: synchronous, allocates; prints the per-role blocked-cycle breakdown
     long long* dprof = nullptr;
-    RFK_CUDA_TRY(cudaMalloc(&dprof, PF_COUNT * sizeof(long long)));
-    RFK_CUDA_TRY(cudaMemsetAsync(dprof, 0, PF_COUNT * sizeof(long long), st));
+    const size_t prof_elems = PF_COUNT + 4 * kTraceLen;
+    RFK_CUDA_TRY(cudaMalloc(&dprof, prof_elems * sizeof(long long)));
+    RFK_CUDA_TRY(cudaMemsetAsync(dprof, 0, prof_elems * sizeof(long long), st));
     P.prof = dprof;
-    fused_ensemble_kernel<true, true><<<grid, kThreads, SMEM_BYTES, st>>>(P);
-    long long hprof[PF_COUNT];
-    RFK_CUDA_TRY(cudaMemcpyAsync(hprof, dprof, sizeof(hprof), cudaMemcpyDeviceToHost, st));
+    P.trace = atoi(prof_env) >= 2 ? dprof + PF_COUNT : nullptr;
+    fused_ensemble_kernel<true, true><<<grid, kThreads, SMEM_BYTES, st>>>(P, x_map);
+    std::vector<long long> hall(prof_elems);
+    RFK_CUDA_TRY(cudaMemcpyAsync(hall.data(), dprof, prof_elems * sizeof(long long), cudaMemcpyDeviceToHost, st));
     RFK_CUDA_TRY(cudaStreamSynchronize(st));
     cudaFree(dprof);
+    const long long* hprof = hall.data();
+    if (P.trace != nullptr) {
+      const char* path = getenv("RFK_FUSED_TRACE_FILE");
+      FILE* f = fopen(path ? path : "fused_trace.txt", "w");
+      if (f) {
+        static const char* roles[4] = {"conv", "load", "mma", "epi"};
+        for (int r = 0; r < 4; ++r)
+          for (int i = 0; i < kTraceLen; ++i) {
+            const long long v = hall[PF_COUNT + r * kTraceLen + i];
+            if (v != 0) fprintf(f, "%s %d %lld %lld\n", roles[r], i, v >> 4, v & 15);
+          }
+        fclose(f);
+      }
+    }
     static const char* names[PF_COUNT] = {"epi:bias_full", "epi:acc1_full", "epi:acc2_full", "epi:acc3_full",
-                                          "epi:TOTAL", "prod:empty", "prod:TOTAL", "w1:empty", "par:bias_free",
-                                          "par:w23_free", "mma:acc1_empty", "mma:full", "mma:w23_full",
-                                          "mma:hid_ready(L2)", "mma:hid_ready(L3)", "mma:TOTAL", "mma:issue(L1)",
-                                          "mma:commit(L1)", "mma:fence(L1)"};
+                                          "epi:TOTAL", "conv:raw_full", "conv:empty", "conv:TOTAL", "load:empty",
+                                          "load:raw_empty", "par:bias_free", "par:w23_free", "mma:acc1_empty",
+                                          "mma:full", "mma:w23_full", "mma:hid_ready(L2)", "mma:hid_ready(L3)",
+                                          "mma:TOTAL"};
     const double items = (double)P.n_tiles * w;
     fprintf(stderr, "[rfk prof] grid %d, items %g; cycles per item (avg over CTAs):\n", grid, items);
     for (int i = 0; i < PF_COUNT; ++i) fprintf(stderr, "[rfk prof]   %-18s %10.0f\n", names[i], hprof[i] / items);
     return RFK_OK;
   }
   if (trials[0]->dtype == RFK_F16)
-    fused_ensemble_kernel<true, false><<<grid, kThreads, SMEM_BYTES, st>>>(P);
+    fused_ensemble_kernel<true, false><<<grid, kThreads, SMEM_BYTES, st>>>(P, x_map);
   else
-    fused_ensemble_kernel<false, false><<<grid, kThreads, SMEM_BYTES, st>>>(P);
+    fused_ensemble_kernel<false, false><<<grid, kThreads, SMEM_BYTES, st>>>(P, x_map);
   RFK_LAUNCH_CHECK("fused_ensemble_kernel");
   return RFK_OK;
 }

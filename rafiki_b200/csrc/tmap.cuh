@@ -1,0 +1,15 @@
+// Host helper: build a CUtensorMap (TMA descriptor) without linking libcuda -- the encoder is
+// fetched from the driver through the runtime (cudaGetDriverEntryPoint).
+#pragma once
+#include <cuda.h>
+
+#include "rfk_common.cuh"
+
+namespace rfk {
+
+// 2-D row-major uint8 tensor [rows, cols] with row pitch `pitch` bytes; box = box_rows x box_cols
+// bytes, no swizzle, out-of-range elements read as zero.
+int make_tmap_u8_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t pitch,
+                    uint32_t box_rows, uint32_t box_cols);
+
+}  // namespace rfk
