@@ -14,8 +14,8 @@
 //
 // Structure (one persistent CTA per SM, 640 threads in five warpgroups, warp-specialised; the
 // epilogue warpgroups take registers the light roles release, setmaxnreg):
-//   warps 0-7   epilogue   TMEM -> registers, bias + ReLU -> 16-bit hidden tile in shared memory
-//                          (the next layer's A operand).  Warps 0-3 own hidden columns 0-63,
+//   warps 0-7   epilogue   TMEM -> registers, bias + ReLU -> 16-bit hidden activations, written back
+//                          to tensor memory (the next layer's A operand: no shared-memory round trip).  Warps 0-3 own hidden columns 0-63,
 //                          warps 4-7 columns 64-127 (a warp may only touch the TMEM lanes
 //                          32*(warp%4)..+31, so two warps share each lane quarter).  Warps 0-3
 //                          also do the last layer: bias + softmax, the running ensemble sum in
@@ -31,6 +31,7 @@
 //                          epilogue of one item overlaps the MMAs of the next; 128 for layer 2;
 //                          16 for layer 3)
 //   warp 18     parameter loader  cp.async.bulk of W2, W3 and the biases of the item's trial
+//   warp 19     MMA issuer for layers 2 and 3 (hidden tile x W2 / W3)
 // A work item is (tile of 128 queries, trial); items of one tile run back to back so the tile
 // stays hot in L2 and the ensemble sum never leaves registers.
 //
@@ -58,8 +59,6 @@ constexpr int CPAD = 16;        // class dimension padded to one UMMA N step
 constexpr int A_STAGE = TILE_M * 128;
 constexpr int B_STAGE = HMAX * 128;
 constexpr int RAW_STAGE = TILE_M * KB;            // 8192 bytes of uint8
-constexpr int HID_ATOM = TILE_M * 128;
-constexpr int HID_BYTES = 2 * HID_ATOM;
 constexpr int W2_BYTES = 2 * HMAX * 128;
 constexpr int W3_BYTES = 2 * CPAD * 128;
 constexpr int BIAS_FLOATS = HMAX + HMAX + CPAD;   // b1 | b2 | b3
@@ -68,33 +67,34 @@ constexpr int BIAS_BYTES = BIAS_FLOATS * 4;
 constexpr int OFF_A = 0;
 constexpr int OFF_B = OFF_A + STAGES * A_STAGE;
 constexpr int OFF_RAW = OFF_B + STAGES * B_STAGE;
-constexpr int OFF_HID = OFF_RAW + RAW_STAGES * RAW_STAGE;
-constexpr int OFF_W2 = OFF_HID + HID_BYTES;
+constexpr int OFF_W2 = OFF_RAW + RAW_STAGES * RAW_STAGE;
 constexpr int OFF_W3 = OFF_W2 + W2_BYTES;
-constexpr int OFF_BIAS = OFF_W3 + W3_BYTES;
+constexpr int OFF_BIAS = OFF_W3 + 2 * W3_BYTES;     // W3 is double buffered by item parity
 constexpr int OFF_BAR = OFF_BIAS + 2 * BIAS_BYTES;
-constexpr int NUM_BARS = 2 * STAGES + 2 * RAW_STAGES + 13;
+constexpr int NUM_BARS = 2 * STAGES + 2 * RAW_STAGES + 17;
 constexpr int OFF_TMEM_SLOT = OFF_BAR + NUM_BARS * 8;
 constexpr int SMEM_USED = OFF_TMEM_SLOT + 16;
 constexpr int SMEM_BYTES = SMEM_USED + 1024;      // slack for the 1024-byte alignment of the base
-static_assert(OFF_HID % 1024 == 0 && OFF_W2 % 1024 == 0 && OFF_W3 % 1024 == 0 && OFF_B % 1024 == 0, "operand alignment");
+static_assert(OFF_W2 % 1024 == 0 && OFF_W3 % 1024 == 0 && OFF_B % 1024 == 0, "operand alignment");
 static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
 
 // Five warpgroups (setmaxnreg works per warpgroup): 0-1 epilogue, 2-3 converters, 4 = loader, MMA
-// issuer, parameter loader and one idle warp.  The kernel starts with 96 registers per thread;
+// issuer for layer 1, parameter loader, MMA issuer for layers 2/3.  The kernel starts with 96 registers per thread;
 // the light roles give registers back and the epilogue warps take them.
 constexpr int kEpiWarps = 8, kConvWarps = 8;
 constexpr int kEpiThreads = kEpiWarps * 32;                   // 256
 constexpr int kConvThreads = kConvWarps * 32;                 // 256: two 16-byte pieces per thread per step
 constexpr int kConvPieces = (TILE_M * KB / 16) / kConvThreads;   // 2
 constexpr int kThreads = (kEpiWarps + kConvWarps + 4) * 32;   // 640
-constexpr int WARP_LOAD = kEpiWarps + kConvWarps, WARP_MMA = WARP_LOAD + 1, WARP_PAR = WARP_LOAD + 2;
+constexpr int WARP_LOAD = kEpiWarps + kConvWarps, WARP_MMA = WARP_LOAD + 1, WARP_PAR = WARP_LOAD + 2,
+              WARP_TAIL = WARP_LOAD + 3;
 constexpr int kRegsEpi = 136, kRegsLight = 56;
 
 constexpr int TMEM_COLS = 512;
 constexpr int COL_ACC1 = 0;     // two buffers of 128 columns
 constexpr int COL_ACC2 = 256;
 constexpr int COL_ACC3 = 384;
+constexpr int COL_HID = 400;     // hidden activations, 16-bit pairs: 64 columns (the next layer's A operand)
 
 struct TrialDev {
   const uint8_t* w1;    // [n_kb][h1_pad] rows of 128 B, swizzled
@@ -118,7 +118,8 @@ struct Bars {
   uint64_t full[STAGES], empty[STAGES];           // A/B operand ring
   uint64_t raw_full[RAW_STAGES], raw_empty[RAW_STAGES];
   uint64_t acc1_full[2], acc1_empty[2];
-  uint64_t hid_ready, acc2_full, acc3_full, w23_full, w23_free;
+  uint64_t hid_ready, acc2_full, acc3_full;
+  uint64_t w2_full, w2_free, w3_full[2], w3_free[2];
   uint64_t bias_full[2], bias_free[2];
 };
 static_assert(sizeof(Bars) == NUM_BARS * 8, "barrier block size");
@@ -164,10 +165,10 @@ __device__ __forceinline__ void sts_u4(uint32_t addr, uint4 v) {
                : "memory");
 }
 
-// 16 accumulator columns of one row -> bias + ReLU -> 16-bit -> two 16-byte chunks of the hidden tile
+// 16 accumulator columns of one row -> bias + ReLU -> 16-bit pairs -> 8 columns of the hidden
+// activations in tensor memory (element k of the row lives in the low/high half of column k/2)
 template <bool kF16>
-__device__ __forceinline__ void hidden_store16(const uint32_t (&v)[16], int c, const float* bias, uint32_t hid_base,
-                                               uint32_t row_off, uint32_t sw) {
+__device__ __forceinline__ void hidden_store16(const uint32_t (&v)[16], int c, const float* bias, uint32_t hid_row_addr) {
   const float4* b4 = reinterpret_cast<const float4*>(bias + c);
   uint32_t p[8];
 #pragma unroll
@@ -176,34 +177,31 @@ __device__ __forceinline__ void hidden_store16(const uint32_t (&v)[16], int c, c
     p[2 * j] = relu_pack_x2<kF16>(__uint_as_float(v[4 * j + 0]) + bb.x, __uint_as_float(v[4 * j + 1]) + bb.y);
     p[2 * j + 1] = relu_pack_x2<kF16>(__uint_as_float(v[4 * j + 2]) + bb.z, __uint_as_float(v[4 * j + 3]) + bb.w);
   }
-  const uint32_t atom = hid_base + (uint32_t)(c >> 6) * HID_ATOM + row_off;
-  const uint32_t ch = (uint32_t)((c & 63) >> 3);
-  sts_u4(atom + (((ch) ^ sw) << 4), make_uint4(p[0], p[1], p[2], p[3]));
-  sts_u4(atom + (((ch + 1) ^ sw) << 4), make_uint4(p[4], p[5], p[6], p[7]));
+  tmem_st8(hid_row_addr + (uint32_t)(c >> 1), p);
 }
 
-// Columns [c_begin, c_end) of one TMEM accumulator row -> hidden tile (A operand of the next
-// layer).  16 columns per step; the TMEM load of step s+1 is in flight while step s is converted
-// and stored (two statically named buffers, so everything stays in registers).
+// Columns [c_begin, c_end) of one TMEM accumulator row -> hidden activations (A operand of the
+// next layer, kept in tensor memory).  16 columns per step; the TMEM load of step s+1 is in flight
+// while step s is converted and stored (two statically named buffers: everything stays in registers).
 template <bool kF16>
 __device__ __forceinline__ void epilogue_hidden(uint32_t tmem_row_addr, int c_begin, int c_end, const float* bias,
-                                                uint32_t hid_base, int row) {
-  if (c_begin >= c_end) return;
-  const uint32_t row_off = (uint32_t)row * 128u;
-  const uint32_t sw = (uint32_t)(row & 7);
-  uint32_t va[16], vb[16];
-  tmem_ld16(tmem_row_addr + (uint32_t)c_begin, va);
-  for (int c = c_begin; c < c_end; c += 32) {
-    tmem_ld_wait();
-    const bool more_b = c + 16 < c_end;
-    if (more_b) tmem_ld16(tmem_row_addr + (uint32_t)c + 16u, vb);
-    hidden_store16<kF16>(va, c, bias, hid_base, row_off, sw);
-    if (more_b) {
+                                                uint32_t hid_row_addr) {
+  if (c_begin < c_end) {
+    uint32_t va[16], vb[16];
+    tmem_ld16(tmem_row_addr + (uint32_t)c_begin, va);
+    for (int c = c_begin; c < c_end; c += 32) {
       tmem_ld_wait();
-      if (c + 32 < c_end) tmem_ld16(tmem_row_addr + (uint32_t)c + 32u, va);
-      hidden_store16<kF16>(vb, c + 16, bias, hid_base, row_off, sw);
+      const bool more_b = c + 16 < c_end;
+      if (more_b) tmem_ld16(tmem_row_addr + (uint32_t)c + 16u, vb);
+      hidden_store16<kF16>(va, c, bias, hid_row_addr);
+      if (more_b) {
+        tmem_ld_wait();
+        if (c + 32 < c_end) tmem_ld16(tmem_row_addr + (uint32_t)c + 32u, va);
+        hidden_store16<kF16>(vb, c + 16, bias, hid_row_addr);
+      }
     }
   }
+  tmem_st_wait();
 }
 
 // kProf (development, RFK_FUSED_PROF=1): the leader thread of each warp role accumulates the
@@ -268,8 +266,12 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
     mbar_init(&bars->hid_ready, kEpiThreads);
     mbar_init(&bars->acc2_full, 1);
     mbar_init(&bars->acc3_full, 1);
-    mbar_init(&bars->w23_full, 1);
-    mbar_init(&bars->w23_free, 1);
+    mbar_init(&bars->w2_full, 1);
+    mbar_init(&bars->w2_free, 1);
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&bars->w3_full[b], 1);
+      mbar_init(&bars->w3_free[b], 1);
+    }
     fence_mbar_init();
   }
   if (warp == WARP_LOAD && lane == 0) tma_prefetch_desc(&x_map);
@@ -296,10 +298,65 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
     const int half = warp >> 2;                                // 0: hidden columns 0-63 + softmax; 1: columns 64-127
     const int row = quarter * 32 + lane;                       // TMEM lane == row of the tile
     const uint32_t lane_addr = tmem_base + ((uint32_t)(quarter * 32) << 16);
-    const uint32_t hid_base = smem_base + OFF_HID;
+    const uint32_t hid_row_addr = lane_addr + COL_HID;
     double acc[CPAD];
 #pragma unroll
     for (int j = 0; j < CPAD; ++j) acc[j] = 0.0;
+    // The softmax of item i-1 is deferred until the layer-1 epilogue of item i has been published:
+    // it then runs while the tensor pipe works on layer 2 of item i instead of sitting on the
+    // item-to-item critical path.  Its accumulator row is pulled into registers first (v3), because
+    // a one-hidden-layer item i may overwrite acc3 as soon as its hidden tile is published.
+    uint32_t v3[16];
+    bool have_prev = false;
+    int prev_tile = 0, prev_t = 0, prev_buf = 0;
+    auto finish_prev = [&]() {
+      // half 0: logits (v3) + bias -> softmax -> running ensemble sum; store the mean after the last trial
+      const float* pbias = reinterpret_cast<const float*>(smem + OFF_BIAS + prev_buf * BIAS_BYTES);
+      if (half == 0) {
+        float z[CPAD];
+        float mx = -INFINITY;
+#pragma unroll
+        for (int j = 0; j < CPAD; ++j) {
+          z[j] = __uint_as_float(v3[j]) + pbias[2 * HMAX + j];
+          if (j < P.n_classes) mx = fmaxf(mx, z[j]);
+        }
+        float sum = 0.f;
+#pragma unroll
+        for (int j = 0; j < CPAD; ++j) {
+          z[j] = j < P.n_classes ? __expf(z[j] - mx) : 0.f;
+          sum += z[j];
+        }
+        const float inv = 1.0f / sum;
+        mbar_arrive(&bars->bias_free[prev_buf]);
+#pragma unroll
+        for (int j = 0; j < CPAD; ++j) acc[j] += (double)(z[j] * inv);
+        if (warp == 0) RFK_TRACE(3, 6);
+        if (prev_t == w - 1) {
+          // the tile's ensemble mean: float64 sum in trial order, one division, one rounding
+          const long long grow = (long long)prev_tile * TILE_M + row;
+          if (grow < P.n) {
+            float* o = P.out + grow * P.n_classes;
+#pragma unroll
+            for (int j = 0; j < CPAD; ++j)
+              if (j < P.n_classes) o[j] = (float)(acc[j] / (double)P.total_trials);
+          }
+#pragma unroll
+          for (int j = 0; j < CPAD; ++j) acc[j] = 0.0;
+        }
+      } else {
+        mbar_arrive(&bars->bias_free[prev_buf]);
+      }
+    };
+    auto fetch_prev_logits = [&](uint32_t parity) {
+      // both halves wait: the hidden tile may not be overwritten before the layer-3 MMAs have read it
+      wait_prof<kProf>(&bars->acc3_full, parity, prof, PF_EPI_ACC3);
+      if (warp == 0) RFK_TRACE(3, 5);
+      tc_fence_after_sync();
+      if (half == 0) {
+        tmem_ld16(lane_addr + COL_ACC3, v3);
+        tmem_ld_wait();
+      }
+    };
     int item = 0;
     uint32_t acc2_phase = 0;          // acc2_full completes one phase per two-hidden-layer item only
     for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
@@ -307,23 +364,24 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
         const TrialDev& T = P.trial[t];
         const int buf = item & 1;
         const uint32_t par2 = (uint32_t)((item >> 1) & 1);
-        const uint32_t par1 = (uint32_t)(item & 1);
         const float* bias = reinterpret_cast<const float*>(smem + OFF_BIAS + buf * BIAS_BYTES);
-        wait_prof<kProf>(&bars->bias_full[buf], par2, prof, PF_EPI_BIAS);
-        // ---- layer 1: acc1[buf] -> hidden
+        if (w > 1 || item < 2) wait_prof<kProf>(&bars->bias_full[buf], par2, prof, PF_EPI_BIAS);
+        // ---- layer 1: acc1[buf] -> hidden (after layer 3 of the previous item has read the hidden tile)
         wait_prof<kProf>(&bars->acc1_full[buf], par2, prof, PF_EPI_ACC1);
         if (warp == 0) RFK_TRACE(3, 1);
+        if (have_prev) fetch_prev_logits((uint32_t)((item - 1) & 1));
         tc_fence_after_sync();
         {
           const int split = T.h1_pad < 64 ? T.h1_pad : 64;
           epilogue_hidden<kF16>(lane_addr + COL_ACC1 + buf * HMAX, half ? split : 0, half ? T.h1_pad : split, bias,
-                                hid_base, row);
+                                hid_row_addr);
         }
         tc_fence_before_sync();
         mbar_arrive(&bars->acc1_empty[buf]);
-        fence_proxy_async_smem();
         mbar_arrive(&bars->hid_ready);
         if (warp == 0) RFK_TRACE(3, 2);
+        // ---- deferred softmax of the previous item, overlapping this item's layer-2 MMAs
+        if (have_prev) finish_prev();
         // ---- layer 2 (two-hidden-layer trials): acc2 -> hidden
         if (T.n_hidden == 2) {
           wait_prof<kProf>(&bars->acc2_full, acc2_phase, prof, PF_EPI_ACC2);
@@ -331,57 +389,22 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
           acc2_phase ^= 1u;
           tc_fence_after_sync();
           const int split = T.h2_pad < 64 ? T.h2_pad : 64;
-          epilogue_hidden<kF16>(lane_addr + COL_ACC2, half ? split : 0, half ? T.h2_pad : split, bias + HMAX, hid_base,
-                                row);
+          epilogue_hidden<kF16>(lane_addr + COL_ACC2, half ? split : 0, half ? T.h2_pad : split, bias + HMAX,
+                                hid_row_addr);
           tc_fence_before_sync();
-          fence_proxy_async_smem();
           mbar_arrive(&bars->hid_ready);
           if (warp == 0) RFK_TRACE(3, 4);
         }
-        // ---- softmax layer: both halves wait (the hidden tile may not be overwritten before the
-        //      layer-3 MMAs have read it); half 0 turns acc3 into probabilities and sums them
-        wait_prof<kProf>(&bars->acc3_full, par1, prof, PF_EPI_ACC3);
-        if (warp == 0) RFK_TRACE(3, 5);
-        tc_fence_after_sync();
-        if (half == 0) {
-          uint32_t v[16];
-          tmem_ld16(lane_addr + COL_ACC3, v);
-          tmem_ld_wait();
-          tc_fence_before_sync();
-          float z[CPAD];
-          float mx = -INFINITY;
-#pragma unroll
-          for (int j = 0; j < CPAD; ++j) {
-            z[j] = __uint_as_float(v[j]) + bias[2 * HMAX + j];
-            if (j < P.n_classes) mx = fmaxf(mx, z[j]);
-          }
-          float sum = 0.f;
-#pragma unroll
-          for (int j = 0; j < CPAD; ++j) {
-            z[j] = j < P.n_classes ? __expf(z[j] - mx) : 0.f;
-            sum += z[j];
-          }
-          const float inv = 1.0f / sum;
-          mbar_arrive(&bars->bias_free[buf]);
-#pragma unroll
-          for (int j = 0; j < CPAD; ++j) acc[j] += (double)(z[j] * inv);
-          if (warp == 0) RFK_TRACE(3, 6);
-        } else {
-          mbar_arrive(&bars->bias_free[buf]);
-        }
+        have_prev = true;
+        prev_tile = tile;
+        prev_t = t;
+        prev_buf = buf;
       }
-      // ---- the tile's ensemble mean: float64 sum in trial order, one division, one rounding
-      if (half == 0) {
-        const long long grow = (long long)tile * TILE_M + row;
-        if (grow < P.n) {
-          float* o = P.out + grow * P.n_classes;
-#pragma unroll
-          for (int j = 0; j < CPAD; ++j)
-            if (j < P.n_classes) o[j] = (float)(acc[j] / (double)P.total_trials);
-        }
-#pragma unroll
-        for (int j = 0; j < CPAD; ++j) acc[j] = 0.0;
-      }
+    }
+    if (have_prev) {
+      fetch_prev_logits((uint32_t)((item - 1) & 1));
+      tc_fence_before_sync();
+      finish_prev();
     }
   } else if (warp < kEpiWarps + kConvWarps) {
     // =============================================================== converter warps
@@ -400,15 +423,18 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
     constexpr uint32_t kRowsPerPass = TILE_M / kConvPieces;      // 64
     int stage = 0, rstage = 0;
     uint32_t phase = 0, rphase = 0;
+    // the probes of step s+1's barriers are issued while step s is converted
+    bool raw_ready = false, slot_ready = false;
     for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
       for (int t = 0; t < w; ++t) {
         for (int kb = 0; kb < n_kb; ++kb) {
-          wait_prof<kProf>(&bars->raw_full[rstage], rphase, prof, PF_CONV_RAW);
+          if (!raw_ready) wait_prof<kProf>(&bars->raw_full[rstage], rphase, prof, PF_CONV_RAW);
           if (warp == kEpiWarps) RFK_TRACE(0, 1);
-          wait_prof<kProf>(&bars->empty[stage], phase ^ 1u, prof, PF_CONV_EMPTY);
+          if (!slot_ready) wait_prof<kProf>(&bars->empty[stage], phase ^ 1u, prof, PF_CONV_EMPTY);
           if (warp == kEpiWarps) RFK_TRACE(0, 2);
           // columns past the end of the row are never read by the MMAs: skip their conversion
           const bool live = !(P.debug & 2) && (kb < n_kb - 1 || q * 16 < last_cols);
+          if (!live) raw_ready = slot_ready = false;
           if (live) {
             const uint32_t rsrc = raw_off + (uint32_t)rstage * RAW_STAGE;
             const uint32_t dlo = a_off_lo + (uint32_t)stage * A_STAGE;
@@ -416,6 +442,11 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
             uint4 raw[kConvPieces];
 #pragma unroll
             for (int it = 0; it < kConvPieces; ++it) raw[it] = lds_u4(rsrc + (uint32_t)it * (kRowsPerPass * KB));
+            {   // look ahead while the loads are in flight
+              const int ns = stage + 1 == STAGES ? 0 : stage + 1, nr = rstage + 1 == RAW_STAGES ? 0 : rstage + 1;
+              raw_ready = mbar_test(&bars->raw_full[nr], nr == 0 ? rphase ^ 1u : rphase);
+              slot_ready = mbar_test(&bars->empty[ns], (ns == 0 ? phase ^ 1u : phase) ^ 1u);
+            }
 #pragma unroll
             for (int it = 0; it < kConvPieces; ++it) {
               const uint4 lo = make_uint4(u8x2_to_op<kF16>(raw[it].x, 0), u8x2_to_op<kF16>(raw[it].x, 2),
@@ -426,7 +457,7 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
               sts_u4(dhi + (uint32_t)it * (kRowsPerPass * 128u), hi);
             }
           }
-          fence_proxy_async_smem();
+          if (!(P.debug & 8)) fence_proxy_async_smem();
           mbar_arrive(&bars->full[stage]);
           mbar_arrive(&bars->raw_empty[rstage]);
           if (warp == kEpiWarps) RFK_TRACE(0, 3);
@@ -436,7 +467,7 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
       }
     }
   } else {
-    // warpgroup 4: loader, MMA issuer, parameter loader, idle warp -- all give registers back
+    // warpgroup 4: loader, two MMA issuers, parameter loader -- all give registers back
     asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsLight));
   }
   if (warp == WARP_LOAD) {
@@ -454,8 +485,12 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
       wait_prof<kProf>(&bars->raw_empty[rstage], rphase ^ 1u, prof, PF_LOAD_RAW_EMPTY);
       RFK_TRACE(1, 1);
       if (lane == 0) {
-        mbar_arrive_expect_tx(&bars->raw_full[rstage], RAW_STAGE);
-        tma_load_2d(smem + OFF_RAW + rstage * RAW_STAGE, &x_map, r_kb * KB, r_tile * TILE_M, &bars->raw_full[rstage]);
+        if (P.debug & 32) {
+          mbar_arrive(&bars->raw_full[rstage]);
+        } else {
+          mbar_arrive_expect_tx(&bars->raw_full[rstage], RAW_STAGE);
+          tma_load_2d(smem + OFF_RAW + rstage * RAW_STAGE, &x_map, r_kb * KB, r_tile * TILE_M, &bars->raw_full[rstage]);
+        }
       }
       __syncwarp();
       if (++rstage == RAW_STAGES) { rstage = 0; rphase ^= 1u; }
@@ -493,83 +528,56 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
     }
   } else if (warp == WARP_PAR) {
     // =============================================================== per-trial parameter loader
-    int item = 0;
+    // biases and W3 are double buffered by item parity; W2 has one buffer, released as soon as
+    // the layer-2 MMAs of the previous item have completed (so its reload overlaps the previous
+    // item's layer-2 epilogue and layer 3).  With a single trial nothing is reloaded.
+    int item = 0, n2 = 0;
     for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
       for (int t = 0; t < w; ++t, ++item) {
         const TrialDev& T = P.trial[t];
         const int buf = item & 1;
-        wait_prof<kProf>(&bars->bias_free[buf], (uint32_t)(((item >> 1) & 1) ^ 1), prof, PF_PAR_BIAS_FREE);
-        if (lane == 0) {
-          mbar_arrive_expect_tx(&bars->bias_full[buf], BIAS_BYTES);
-          bulk_g2s(smem + OFF_BIAS + buf * BIAS_BYTES, T.bias, BIAS_BYTES, &bars->bias_full[buf]);
+        const uint32_t par_free2 = (uint32_t)(((item >> 1) & 1) ^ 1);
+        if (w > 1 || item < 2) {
+          wait_prof<kProf>(&bars->bias_free[buf], par_free2, prof, PF_PAR_BIAS_FREE);
+          if (lane == 0) {
+            mbar_arrive_expect_tx(&bars->bias_full[buf], BIAS_BYTES);
+            bulk_g2s(smem + OFF_BIAS + buf * BIAS_BYTES, T.bias, BIAS_BYTES, &bars->bias_full[buf]);
+          }
+          __syncwarp();
+          wait_prof<kProf>(&bars->w3_free[buf], par_free2, prof, PF_PAR_W23_FREE);
+          const int hl_pad = T.n_hidden == 2 ? T.h2_pad : T.h1_pad;
+          const uint32_t w3_bytes = (uint32_t)((hl_pad + 63) / 64) * CPAD * 128u;
+          if (lane == 0) {
+            mbar_arrive_expect_tx(&bars->w3_full[buf], w3_bytes);
+            bulk_g2s(smem + OFF_W3 + buf * W3_BYTES, T.w3, w3_bytes, &bars->w3_full[buf]);
+          }
+          __syncwarp();
         }
-        __syncwarp();
-        wait_prof<kProf>(&bars->w23_free, (uint32_t)((item & 1) ^ 1), prof, PF_PAR_W23_FREE);
-        const int hl_pad = T.n_hidden == 2 ? T.h2_pad : T.h1_pad;
-        const uint32_t w3_bytes = (uint32_t)((hl_pad + 63) / 64) * CPAD * 128u;
-        const uint32_t w2_bytes = T.n_hidden == 2 ? (uint32_t)((T.h1_pad + 63) / 64) * (uint32_t)T.h2_pad * 128u : 0u;
-        if (lane == 0) {
-          mbar_arrive_expect_tx(&bars->w23_full, w2_bytes + w3_bytes);
-          if (w2_bytes) bulk_g2s(smem + OFF_W2, T.w2, w2_bytes, &bars->w23_full);
-          bulk_g2s(smem + OFF_W3, T.w3, w3_bytes, &bars->w23_full);
+        if (T.n_hidden == 2) {
+          if (w > 1 || n2 == 0) {
+            wait_prof<kProf>(&bars->w2_free, (uint32_t)((n2 & 1) ^ 1), prof, PF_PAR_W23_FREE);
+            const uint32_t w2_bytes = (uint32_t)((T.h1_pad + 63) / 64) * (uint32_t)T.h2_pad * 128u;
+            if (lane == 0) {
+              mbar_arrive_expect_tx(&bars->w2_full, w2_bytes);
+              bulk_g2s(smem + OFF_W2, T.w2, w2_bytes, &bars->w2_full);
+            }
+            __syncwarp();
+          }
+          ++n2;
         }
-        __syncwarp();
       }
     }
   } else if (warp == WARP_MMA) {
-    // =============================================================== MMA issuer
-    // Everything below is executed by all 32 lanes in lock step (mbarrier waits included); the
-    // *_elect helpers pick one lane per statement, so there is no divergent region at all.
-    // Descriptors are a constant upper word plus (address >> 4) in the lower word.
+    // =============================================================== MMA issuer, layer 1
+    // Executed by all 32 lanes in lock step (mbarrier waits included); the *_elect helpers pick
+    // one lane per statement, so there is no divergent region.  Descriptors are a constant upper
+    // word plus (address >> 4) in the lower word.  The probe of the NEXT stage's barrier is
+    // issued before this stage's commit so that its latency hides behind the commit.
     int stage = 0;
-    uint32_t phase = 0, hid_phase = 0;
+    uint32_t phase = 0;
     const uint32_t a_lo0 = desc_lo_sw128(smem_base + OFF_A), b_lo0 = desc_lo_sw128(smem_base + OFF_B);
-    const uint32_t hid_lo = desc_lo_sw128(smem_base + OFF_HID);
-    const uint32_t w2_lo = desc_lo_sw128(smem_base + OFF_W2), w3_lo = desc_lo_sw128(smem_base + OFF_W3);
-    // layers 2/3 of a finished layer-1 item still to be issued: pend 1 = layer 2 next, 2 = layer 3 next
-    int pend = 0, pend_item = 0, pend_t = 0;
-    auto issue_small_layer = [&](uint32_t d_tmem, uint32_t b_lo, uint32_t b_atom, uint32_t idesc, int ksteps) {
-      // hidden tile (A) x small weight matrix (B); K runs over 64-wide atoms of 4 steps each
-      for (int k0 = 0; k0 < ksteps; k0 += 4) {
-        const uint32_t a = hid_lo + (uint32_t)(k0 >> 2) * (HID_ATOM >> 4);
-        const uint32_t b = b_lo + (uint32_t)(k0 >> 2) * b_atom;
-        mma4_f16_ss_elect(d_tmem, desc_from_lo(a), desc_from_lo(b), idesc, k0 != 0, ksteps - k0 < 4 ? ksteps - k0 : 4);
-      }
-    };
-    auto issue_layer2 = [&]() {
-      const TrialDev& T = P.trial[pend_t];
-      wait_prof<kProf>(&bars->w23_full, (uint32_t)(pend_item & 1), prof, PF_MMA_W23_FULL);
-      wait_prof<kProf>(&bars->hid_ready, hid_phase, prof, PF_MMA_HID_L2);
-      hid_phase ^= 1u;
-      tc_fence_after_sync();
-      issue_small_layer(tmem_base + COL_ACC2, w2_lo, ((uint32_t)T.h2_pad * 128u) >> 4,
-                        idesc_16bit_f32(kF16, TILE_M, T.h2_pad), T.h1_pad >> 4);
-      mma_commit_elect(&bars->acc2_full);
-      pend = 2;
-    };
-    auto issue_layer3 = [&]() {
-      const TrialDev& T = P.trial[pend_t];
-      if (T.n_hidden != 2) wait_prof<kProf>(&bars->w23_full, (uint32_t)(pend_item & 1), prof, PF_MMA_W23_FULL);
-      wait_prof<kProf>(&bars->hid_ready, hid_phase, prof, PF_MMA_HID_L3);
-      hid_phase ^= 1u;
-      tc_fence_after_sync();
-      const int hl_pad = T.n_hidden == 2 ? T.h2_pad : T.h1_pad;
-      issue_small_layer(tmem_base + COL_ACC3, w3_lo, (CPAD * 128u) >> 4, idesc_16bit_f32(kF16, TILE_M, CPAD),
-                        hl_pad >> 4);
-      mma_commit_elect(&bars->acc3_full);
-      mma_commit_elect(&bars->w23_free);
-      pend = 0;
-    };
-    // Layers 2/3 of the previous item are slipped into this item's layer-1 K loop as soon as the
-    // epilogue has published their input (non-blocking probe); whatever is left is finished,
-    // blocking, after the loop.
-    auto poll_pending = [&]() {
-      if (pend != 0 && mbar_test(&bars->hid_ready, hid_phase)) {
-        if (pend == 1) issue_layer2();
-        else issue_layer3();
-      }
-    };
     const int last_ksteps = (P.d - (n_kb - 1) * KB) >> 4;      // K steps of the ragged last block (1..4)
+    bool next_ready = false;
     int item = 0;
     for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
       for (int t = 0; t < w; ++t, ++item) {
@@ -580,7 +588,7 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
         wait_prof<kProf>(&bars->acc1_empty[buf], (uint32_t)(((item >> 1) & 1) ^ 1), prof, PF_MMA_ACC1_EMPTY);
         tc_fence_after_sync();
         for (int kb = 0; kb < n_kb; ++kb) {
-          wait_prof<kProf>(&bars->full[stage], phase, prof, PF_MMA_FULL);
+          if (!next_ready) wait_prof<kProf>(&bars->full[stage], phase, prof, PF_MMA_FULL);
           RFK_TRACE(2, 1);
           tc_fence_after_sync();
           const int ksteps = kb == n_kb - 1 ? last_ksteps : 4;
@@ -590,29 +598,60 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
             mma4_f16_ss_elect(d_tmem, desc_from_lo(a), desc_from_lo(b), idesc1, kb != 0, ksteps);
           }
           RFK_TRACE(2, 2);
-          mma_commit_elect(&bars->empty[stage]);
+          const int cur = stage;
+          if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+          next_ready = mbar_test(&bars->full[stage], phase);
+          mma_commit_elect(&bars->empty[cur]);
           if (kb == n_kb - 1) mma_commit_elect(&bars->acc1_full[buf]);
           RFK_TRACE(2, 3);
-          if (++stage == STAGES) { stage = 0; phase ^= 1u; }
-          poll_pending();
-          RFK_TRACE(2, 4);
         }
-        while (pend != 0) {                          // finish the previous item before queueing this one's tail
-          if (pend == 1) issue_layer2();
-          else issue_layer3();
-        }
-        pend = T.n_hidden == 2 ? 1 : 2;
-        pend_item = item;
-        pend_t = t;
       }
     }
-    while (pend != 0) {
-      if (pend == 1) issue_layer2();
-      else issue_layer3();
+  } else if (warp == WARP_TAIL) {
+    // =============================================================== MMA issuer, layers 2 and 3
+    // hidden tile (A, written by the epilogue warps) x W2 / W3 (B, parameter loader).  A separate
+    // warp, so that the layer-1 issuer never waits for an epilogue; the tensor pipe interleaves
+    // the two instruction streams, which touch disjoint accumulators.
+    uint32_t hid_phase = 0;
+    const uint32_t w2_lo = desc_lo_sw128(smem_base + OFF_W2), w3_lo = desc_lo_sw128(smem_base + OFF_W3);
+    auto issue_small_layer = [&](uint32_t d_tmem, uint32_t b_lo, uint32_t b_atom, uint32_t idesc, int ksteps) {
+      // A = hidden activations in tensor memory (8 columns per K step); B in 64-wide atoms of 4 steps
+      for (int k0 = 0; k0 < ksteps; k0 += 4) {
+        const uint32_t a = tmem_base + COL_HID + (uint32_t)k0 * 8u;
+        const uint32_t b = b_lo + (uint32_t)(k0 >> 2) * b_atom;
+        mma4_f16_ts_elect(d_tmem, a, desc_from_lo(b), idesc, k0 != 0, ksteps - k0 < 4 ? ksteps - k0 : 4);
+      }
+    };
+    int item = 0, n2 = 0;
+    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
+      for (int t = 0; t < w; ++t, ++item) {
+        const TrialDev& T = P.trial[t];
+        const int buf = item & 1;
+        if (T.n_hidden == 2) {
+          if (w > 1 || n2 == 0) wait_prof<kProf>(&bars->w2_full, (uint32_t)(n2 & 1), prof, PF_MMA_W23_FULL);
+          ++n2;
+          wait_prof<kProf>(&bars->hid_ready, hid_phase, prof, PF_MMA_HID_L2);
+          hid_phase ^= 1u;
+          tc_fence_after_sync();
+          issue_small_layer(tmem_base + COL_ACC2, w2_lo, ((uint32_t)T.h2_pad * 128u) >> 4,
+                            idesc_16bit_f32(kF16, TILE_M, T.h2_pad), T.h1_pad >> 4);
+          mma_commit_elect(&bars->acc2_full);
+          mma_commit_elect(&bars->w2_free);
+        }
+        if (w > 1 || item < 2) wait_prof<kProf>(&bars->w3_full[buf], (uint32_t)((item >> 1) & 1), prof, PF_MMA_W23_FULL);
+        wait_prof<kProf>(&bars->hid_ready, hid_phase, prof, PF_MMA_HID_L3);
+        hid_phase ^= 1u;
+        tc_fence_after_sync();
+        const int hl_pad = T.n_hidden == 2 ? T.h2_pad : T.h1_pad;
+        issue_small_layer(tmem_base + COL_ACC3, w3_lo + (uint32_t)buf * (W3_BYTES >> 4), (CPAD * 128u) >> 4,
+                          idesc_16bit_f32(kF16, TILE_M, CPAD), hl_pad >> 4);
+        mma_commit_elect(&bars->acc3_full);
+        mma_commit_elect(&bars->w3_free[buf]);
+      }
     }
   }
   if (kProf && P.prof != nullptr && lane == 0 &&
-      (warp == 0 || warp == kEpiWarps || warp == WARP_LOAD || warp == WARP_MMA || warp == WARP_PAR)) {
+      (warp == 0 || warp == kEpiWarps || warp == WARP_LOAD || warp == WARP_MMA || warp == WARP_PAR || warp == WARP_TAIL)) {
     const long long total = clock64() - t_start;
     if (warp == 0) prof[PF_EPI_TOTAL] = total;
     if (warp == kEpiWarps) prof[PF_CONV_TOTAL] = total;

@@ -137,6 +137,13 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
       : "r"(taddr)
       : "memory");
 }
+// 32 lanes x 8 consecutive 32-bit columns, registers -> TMEM: thread i writes lane (base_lane + i).
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t (&v)[8]) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(taddr), "r"(v[0]),
+               "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
+               : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // ------------------------------------------------------------------------ tcgen05.mma
@@ -214,6 +221,31 @@ __device__ __forceinline__ void mma4_f16_ss_elect(uint32_t d_tmem, uint64_t a_de
       "@q3 tcgen05.mma.cta_group::1.kind::f16 [%0], a3, b3, %3, t;\n\t"
       "@q4 tcgen05.mma.cta_group::1.kind::f16 [%0], a4, b4, %3, t;\n\t}" ::"r"(d_tmem),
       "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate_first), "r"(nsteps)
+      : "memory");
+}
+// Same, with the A operand in tensor memory ("TS" form): A is 128 lanes x (K/2) 32-bit columns,
+// two consecutive K elements per cell, so a 16-element K step is +8 columns; B stays in shared
+// memory (+2 on the descriptor per step).
+__device__ __forceinline__ void mma4_f16_ts_elect(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc,
+                                                   uint32_t accumulate_first, int nsteps) {
+  asm volatile(
+      "{\n\t.reg .pred p, q, q2, q3, q4, t;\n\t"
+      ".reg .b64 b2, b3, b4;\n\t"
+      ".reg .b32 a2, a3, a4;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "setp.eq.u32 t, 0, 0;\n\t"
+      "setp.gt.and.s32 q2, %5, 1, q;\n\t"
+      "setp.gt.and.s32 q3, %5, 2, q;\n\t"
+      "setp.gt.and.s32 q4, %5, 3, q;\n\t"
+      "add.u32 a2, %1, 8;\n\tadd.u64 b2, %2, 2;\n\t"
+      "add.u32 a3, %1, 16;\n\tadd.u64 b3, %2, 4;\n\t"
+      "add.u32 a4, %1, 24;\n\tadd.u64 b4, %2, 6;\n\t"
+      "@q  tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t"
+      "@q2 tcgen05.mma.cta_group::1.kind::f16 [%0], [a2], b2, %3, t;\n\t"
+      "@q3 tcgen05.mma.cta_group::1.kind::f16 [%0], [a3], b3, %3, t;\n\t"
+      "@q4 tcgen05.mma.cta_group::1.kind::f16 [%0], [a4], b4, %3, t;\n\t}" ::"r"(d_tmem),
+      "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate_first), "r"(nsteps)
       : "memory");
 }
 __device__ __forceinline__ void mma_commit_elect(uint64_t* bar) {

@@ -6,13 +6,14 @@ from rafiki_b200 import engine, synth
 
 def main():
     torch.cuda.set_device(0)
-    dead = synth.dead_mask(784)
+    S = int(os.environ.get('RFK_S', '28'))
+    dead = synth.dead_mask(S * S)
     cases = [(1, 65536), (8, 65536)] if len(sys.argv) < 2 else [tuple(int(v) for v in a.split('x')) for a in sys.argv[1:]]
     for w, n in cases:
         H = int(os.environ.get('RFK_H', '128'))
-        trials = [engine.Trial(synth.make_trial(t, 28, 1, 2, H, dead=dead)) for t in range(w)]
+        trials = [engine.Trial(synth.make_trial(t, S, 1, 2, H, dead=dead)) for t in range(w)]
         ens = engine.Ensemble(trials)
-        xs = [torch.from_numpy(synth.make_queries(n, 28, 1, 'uniform', seed=i, dead=dead)).cuda() for i in range(4)]
+        xs = [torch.from_numpy(synth.make_queries(n, S, 1, 'uniform', seed=i, dead=dead)).cuda() for i in range(4)]
         out = torch.empty((n, 10), dtype=torch.float32, device='cuda')
         for i in range(3):
             ens.forward(xs[i % 4], out=out)
