@@ -38,6 +38,8 @@ WORKLOADS = {
                name='8-trial TfFeedForward ensemble, 28x28, batch 65536 (BASELINE configs[2])'),
     'c2': dict(trials=3, batch=4096, image_size=28, channels=1, hidden=128, layers=2, scaling='weak',
                name='3-trial TfFeedForward ensemble, 28x28, batch 4096 per GPU (BASELINE configs[1])'),
+    'c5': dict(trials=3, batch=65536, image_size=28, channels=1, hidden=128, layers=2, scaling='weak', sweep=True,
+               name='serving latency sweep, batch 1..65536, 3-trial ensemble (BASELINE configs[4])'),
 }
 L2_BYTES = 126 * 1024 * 1024
 FALLBACK_PEAKS = {'hbm_gbs': 6650.0, 'bf16_tflops': 1590.0, 'bf16_tflops_sustained': 1400.0}
@@ -149,6 +151,46 @@ def run_reference(args, wl):
     return 0
 
 
+def run_latency_sweep(args, wl, ens, xs, out, params, rank):
+    """BASELINE configs[4]: p50 / p99 latency and queries/s per batch size, 3-trial ensemble."""
+    import torch
+    rows = []
+    n_max = wl['batch']
+    sizes = [1 << k for k in range(0, 17) if (1 << k) <= n_max]
+    for bsz in sizes:
+        x = [b[:bsz].contiguous() for b in xs]
+        o = out[:bsz]
+        for i in range(20):
+            ens.forward(x[i % len(x)], out=o)
+        torch.cuda.synchronize()
+        lat = []
+        for i in range(max(args.steps, 200)):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            ens.forward(x[i % len(x)], out=o)
+            b.record()
+            b.synchronize()
+            lat.append(a.elapsed_time(b))
+        lat.sort()
+        p50, p99 = lat[len(lat) // 2], lat[min(len(lat) - 1, int(len(lat) * 0.99))]
+        rows.append({'batch': bsz, 'p50_ms': p50, 'p99_ms': p99, 'queries_per_s_at_p50': bsz / (p50 * 1e-3)})
+    if rank == 0:
+        cores = os.cpu_count() or 1
+        cpu_rows = []
+        if not args.no_cpu_baseline:
+            for bsz in (1, 32, 1024):
+                rate, times = cpu_oracle_rate(params, xs[0].cpu().numpy(), bsz, 3, cores)
+                cpu_rows.append({'batch': bsz, 'ms': min(times) * 1e3, 'queries_per_s': rate})
+        print(json.dumps({'metric': 'ensemble_batch_latency_ms', 'unit': 'ms', 'higher_is_better': False,
+                          'n_gpus': 1, 'dtype': args.compute, 'data': 'synthetic',
+                          'config': {'workload': wl['name'], 'trials': wl['trials']},
+                          'value': rows[-1]['p99_ms'], 'sweep': rows,
+                          'cpu_baseline': {'kind': 'port', 'cores': cores, 'unit': 'ms', 'rows': cpu_rows,
+                                           'sample': 'oracle serve_batch on the first b queries, best of 3'}}),
+              flush=True)
+    return 0
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
@@ -187,17 +229,22 @@ def main():
         mine = [t for t in range(W) if t % world == rank]
     else:                              # independent replicas
         mine = list(range(W))
+    from rafiki_b200.distributed import DistributedEnsemble
     trials = [engine.Trial(params[t], compute=args.compute) for t in mine]
     ens = engine.Ensemble(trials, total_trials=W) if trials else None
     xs = [torch.from_numpy(b).to(dev) for b in batches]
     out = torch.zeros((n, C), dtype=torch.float32, device=dev)
     do_reduce = world > 1 and wl['scaling'] == 'strong'
+    dens = DistributedEnsemble(ens, W, C, dev, root=0) if do_reduce else None
 
     def step(i):
-        if ens is not None:
+        if dens is not None:
+            dens.forward(xs[i % len(xs)], out=out)       # local fused kernel + NCCL reduce onto rank 0
+        elif ens is not None:
             ens.forward(xs[i % len(xs)], out=out)
-        if do_reduce:
-            dist.reduce(out, dst=0, op=dist.ReduceOp.SUM)
+
+    if wl.get('sweep'):
+        return run_latency_sweep(args, wl, ens, xs, out, params, rank)
 
     def barrier():
         if world > 1:
@@ -223,6 +270,19 @@ def main():
         ms = float(t.item())
     units = n * args.steps * (world if wl['scaling'] == 'weak' else 1)
     value = units / (ms * 1e-3)
+
+    # ---- per-batch latency (the metric's "p99 batch latency"): one step at a time, device timed
+    lat = []
+    for i in range(min(args.steps, 200)):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        step(i)
+        b.record()
+        b.synchronize()
+        lat.append(a.elapsed_time(b))
+    lat.sort()
+    latency = {'p50_ms': lat[len(lat) // 2], 'p99_ms': lat[min(len(lat) - 1, int(len(lat) * 0.99))],
+               'samples': len(lat), 'what': 'one batch, device resident, CUDA events'}
 
     # ---- end to end: pinned host -> device -> pinned host, three batches in flight
     e2e = None
@@ -285,6 +345,7 @@ def main():
                        'l2': 'rotating over {} distinct resident batches ({} MB > L2)'.format(
                            len(xs), len(xs) * n * d // (1 << 20))},
             'clocks': clocks,
+            'latency': latency,
             'e2e': e2e,
             'gpu_launches': args.steps * (1 if ens is not None else 0),
             'roofline': {'bound': 'tensor', 'achieved': achieved, 'peak': peak, 'unit': 'TFLOP/s',
