@@ -237,11 +237,25 @@ def main():
     do_reduce = world > 1 and wl['scaling'] == 'strong'
     dens = DistributedEnsemble(ens, W, C, dev, root=0) if do_reduce else None
 
+    outs = [out, torch.zeros_like(out)]
+    pending = [None, None]
+
     def step(i):
         if dens is not None:
-            dens.forward(xs[i % len(xs)], out=out)       # local fused kernel + NCCL reduce onto rank 0
+            # local fused kernel + NCCL reduce onto rank 0; two result buffers in turn, so the
+            # reduce of batch i overlaps the kernel of batch i+1
+            slot = i & 1
+            if pending[slot] is not None:
+                pending[slot].wait()
+            pending[slot] = dens.forward_async(xs[i % len(xs)], outs[slot])
         elif ens is not None:
             ens.forward(xs[i % len(xs)], out=out)
+
+    def drain():
+        for k in range(2):
+            if pending[k] is not None:
+                pending[k].wait()
+                pending[k] = None
 
     if wl.get('sweep'):
         return run_latency_sweep(args, wl, ens, xs, out, params, rank)
@@ -253,6 +267,7 @@ def main():
 
     for i in range(max(args.warmup, 3)):
         step(i)
+    drain()
     barrier()
     sampler = ClockSampler(local_rank) if rank == 0 else None
     if sampler:
@@ -261,6 +276,7 @@ def main():
     e0.record()
     for i in range(args.steps):
         step(i)
+    drain()
     e1.record()
     barrier()
     ms = e0.elapsed_time(e1)
@@ -277,6 +293,7 @@ def main():
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
         step(i)
+        drain()
         b.record()
         b.synchronize()
         lat.append(a.elapsed_time(b))
@@ -286,7 +303,30 @@ def main():
 
     # ---- end to end: pinned host -> device -> pinned host, three batches in flight
     e2e = None
-    if ens is not None:
+    if dens is not None:
+        # every rank: pinned host batch -> device -> fused kernel -> reduce; rank 0: result -> pinned host
+        h_in = torch.from_numpy(batches[0]).pin_memory()
+        d_in = torch.empty_like(xs[0])
+        h_out = torch.empty((n, C), dtype=torch.float32).pin_memory()
+        e2e_steps = max(4, min(args.steps, 40))
+        for it in range(2 + e2e_steps):
+            if it == 2:
+                barrier()
+                t0 = time.perf_counter()
+            d_in.copy_(h_in, non_blocking=True)
+            dens.forward(d_in, out=out)
+            if rank == 0:
+                h_out.copy_(out, non_blocking=True)
+        barrier()
+        dt = time.perf_counter() - t0
+        t = torch.tensor([dt], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dt = float(t.item())
+        e2e = {'value': n * e2e_steps / dt, 'unit': 'queries/s', 'h2d_bytes_per_step': n * d * world,
+               'd2h_bytes_per_step': n * C * 4, 'steps': e2e_steps,
+               'note': 'every rank uploads the whole uint8 batch from pinned host memory (its own PCIe link), '
+                       'fused kernel, NCCL reduce, rank 0 downloads the probabilities'}
+    elif ens is not None:
         depth = 3
         pipe = engine.HostPipeline(ens, max_batch=n, depth=depth)
         for s in range(depth):
@@ -315,8 +355,7 @@ def main():
         e_units = n * e2e_steps * (world if wl['scaling'] == 'weak' else 1)
         e2e = {'value': e_units / dt, 'unit': 'queries/s', 'h2d_bytes_per_step': pipe.h2d_bytes,
                'd2h_bytes_per_step': pipe.d2h_bytes, 'steps': e2e_steps, 'slots_in_flight': depth,
-               'note': 'per rank: H2D of the whole uint8 batch + fused kernel + D2H of the probabilities'
-                       + ('; cross-rank reduce not included' if do_reduce else '')}
+               'note': 'per rank: H2D of the whole uint8 batch + fused kernel + D2H of the probabilities'}
     clocks = sampler.stop() if sampler else None
 
     if rank == 0:

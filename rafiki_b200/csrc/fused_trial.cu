@@ -111,6 +111,7 @@ struct FusedParams {
   int d, n_kb, w, total_trials, n_classes, n_tiles;
   long long* prof;   // development only (RFK_FUSED_PROF): PF_COUNT counters, summed over CTAs
   long long* trace;  // development only (RFK_FUSED_PROF=2): block 0 event timestamps, [4 roles][kTraceLen]
+  int split;         // 1: one (tile, trial) item per CTA, per-trial probabilities to out[t][n][C] (small batches)
   int debug;         // development only (RFK_FUSED_DEBUG): 1 skip W1 copies, 2 skip conversion, 4 skip layer-1 MMAs
 };
 
@@ -288,7 +289,14 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
   constexpr uint32_t tmem_base = 0u;
 
   const int n_kb = P.n_kb;
-  const int w = P.w;
+  // Work assignment.  Normal: CTA b takes tiles b, b + grid, ... and runs all trials of a tile back
+  // to back.  Split (small batches): CTA b is exactly one item, tile b / W, trial b % W, so that the
+  // trials of a tile run on different SMs at the same time; kernel 3 then averages the W outputs.
+  const int tile0 = P.split ? (int)blockIdx.x / P.w : (int)blockIdx.x;
+  const int tile_step = P.split ? P.n_tiles : (int)gridDim.x;
+  const int t0 = P.split ? (int)blockIdx.x % P.w : 0;
+  const int t1 = P.split ? t0 + 1 : P.w;
+  const int w = t1 - t0;                       // trials this CTA runs per tile
   const uint32_t smem_base = smem_u32(smem);
 
   if (warp < kEpiWarps) {
@@ -331,14 +339,14 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
 #pragma unroll
         for (int j = 0; j < CPAD; ++j) acc[j] += (double)(z[j] * inv);
         if (warp == 0) RFK_TRACE(3, 6);
-        if (prev_t == w - 1) {
+        if (prev_t == t1 - 1) {
           // the tile's ensemble mean: float64 sum in trial order, one division, one rounding
           const long long grow = (long long)prev_tile * TILE_M + row;
           if (grow < P.n) {
-            float* o = P.out + grow * P.n_classes;
+            float* o = P.out + (P.split ? (long long)t0 * P.n * P.n_classes : 0ll) + grow * P.n_classes;
 #pragma unroll
             for (int j = 0; j < CPAD; ++j)
-              if (j < P.n_classes) o[j] = (float)(acc[j] / (double)P.total_trials);
+              if (j < P.n_classes) o[j] = (float)(acc[j] / (double)(P.split ? 1 : P.total_trials));
           }
 #pragma unroll
           for (int j = 0; j < CPAD; ++j) acc[j] = 0.0;
@@ -359,8 +367,8 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
     };
     int item = 0;
     uint32_t acc2_phase = 0;          // acc2_full completes one phase per two-hidden-layer item only
-    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
-      for (int t = 0; t < w; ++t, ++item) {
+    for (int tile = tile0; tile < P.n_tiles; tile += tile_step) {
+      for (int t = t0; t < t1; ++t, ++item) {
         const TrialDev& T = P.trial[t];
         const int buf = item & 1;
         const uint32_t par2 = (uint32_t)((item >> 1) & 1);
@@ -425,8 +433,8 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
     uint32_t phase = 0, rphase = 0;
     // the probes of step s+1's barriers are issued while step s is converted
     bool raw_ready = false, slot_ready = false;
-    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
-      for (int t = 0; t < w; ++t) {
+    for (int tile = tile0; tile < P.n_tiles; tile += tile_step) {
+      for (int t = t0; t < t1; ++t) {
         for (int kb = 0; kb < n_kb; ++kb) {
           if (!raw_ready) wait_prof<kProf>(&bars->raw_full[rstage], rphase, prof, PF_CONV_RAW);
           if (warp == kEpiWarps) RFK_TRACE(0, 1);
@@ -477,10 +485,10 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
     int stage = 0, rstage = 0;
     uint32_t phase = 0, rphase = 0;
     int my_tiles = 0;
-    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) ++my_tiles;
+    for (int tile = tile0; tile < P.n_tiles; tile += tile_step) ++my_tiles;
     const int total_steps = my_tiles * w * n_kb;
     // raw cursor (runs ahead)
-    int r_tile = blockIdx.x, r_t = 0, r_kb = 0, r_step = 0;
+    int r_tile = tile0, r_t = t0, r_kb = 0, r_step = 0;
     auto issue_raw = [&]() {
       wait_prof<kProf>(&bars->raw_empty[rstage], rphase ^ 1u, prof, PF_LOAD_RAW_EMPTY);
       RFK_TRACE(1, 1);
@@ -497,15 +505,15 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
       ++r_step;
       if (++r_kb == n_kb) {
         r_kb = 0;
-        if (++r_t == w) {
-          r_t = 0;
-          r_tile += gridDim.x;
+        if (++r_t == t1) {
+          r_t = t0;
+          r_tile += tile_step;
         }
       }
     };
     for (int i = 0; i < RAW_STAGES - 1 && r_step < total_steps; ++i) issue_raw();
-    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
-      for (int t = 0; t < w; ++t) {
+    for (int tile = tile0; tile < P.n_tiles; tile += tile_step) {
+      for (int t = t0; t < t1; ++t) {
         const TrialDev& T = P.trial[t];
         const uint32_t bytes = (uint32_t)T.h1_pad * 128u;
         const uint8_t* src = T.w1;
@@ -532,8 +540,8 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
     // the layer-2 MMAs of the previous item have completed (so its reload overlaps the previous
     // item's layer-2 epilogue and layer 3).  With a single trial nothing is reloaded.
     int item = 0, n2 = 0;
-    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
-      for (int t = 0; t < w; ++t, ++item) {
+    for (int tile = tile0; tile < P.n_tiles; tile += tile_step) {
+      for (int t = t0; t < t1; ++t, ++item) {
         const TrialDev& T = P.trial[t];
         const int buf = item & 1;
         const uint32_t par_free2 = (uint32_t)(((item >> 1) & 1) ^ 1);
@@ -579,8 +587,8 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
     const int last_ksteps = (P.d - (n_kb - 1) * KB) >> 4;      // K steps of the ragged last block (1..4)
     bool next_ready = false;
     int item = 0;
-    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
-      for (int t = 0; t < w; ++t, ++item) {
+    for (int tile = tile0; tile < P.n_tiles; tile += tile_step) {
+      for (int t = t0; t < t1; ++t, ++item) {
         const TrialDev& T = P.trial[t];
         const int buf = item & 1;
         const uint32_t idesc1 = idesc_16bit_f32(kF16, TILE_M, T.h1_pad);
@@ -623,8 +631,8 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
       }
     };
     int item = 0, n2 = 0;
-    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
-      for (int t = 0; t < w; ++t, ++item) {
+    for (int tile = tile0; tile < P.n_tiles; tile += tile_step) {
+      for (int t = t0; t < t1; ++t, ++item) {
         const TrialDev& T = P.trial[t];
         const int buf = item & 1;
         if (T.n_hidden == 2) {
@@ -751,8 +759,15 @@ void fused_release(rfk_mlp* h) {
   h->fused = nullptr;
 }
 
+size_t fused_workspace_bytes(int w, int n_classes, int64_t n) {
+  // split mode (see the kernel): used when all (tile, trial) items fit on the GPU at once
+  const int64_t n_tiles = (n + TILE_M - 1) / TILE_M;
+  if (w > 1 && n_tiles * w <= (int64_t)num_sms()) return (size_t)w * (size_t)n * n_classes * sizeof(float);
+  return 0;
+}
+
 int fused_forward(rfk_mlp* const* trials, int w, int total_trials, const uint8_t* x, int64_t n, float* out,
-                  cudaStream_t st) {
+                  void* ws, size_t ws_bytes, cudaStream_t st) {
   RFK_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0, "fused forward: x must be 16-byte aligned");
   const int d = trials[0]->d;
   // TMA descriptor of the query batch: uint8 [n, d]; one box = 128 rows x 64 bytes
@@ -781,7 +796,14 @@ int fused_forward(rfk_mlp* const* trials, int w, int total_trials, const uint8_t
     P.debug = dbg ? atoi(dbg) : 0;
   }
   const int sms = num_sms();
-  const int grid = P.n_tiles < sms ? P.n_tiles : sms;
+  int grid = P.n_tiles < sms ? P.n_tiles : sms;
+  const size_t split_bytes = fused_workspace_bytes(w, P.n_classes, n);
+  const bool split = split_bytes != 0 && ws != nullptr && ws_bytes >= split_bytes && getenv("RFK_NO_SPLIT") == nullptr;
+  if (split) {
+    P.split = 1;
+    P.out = static_cast<float*>(ws);
+    grid = P.n_tiles * w;
+  }
   const char* prof_env = getenv("RFK_FUSED_PROF");
   if (prof_env != nullptr && atoi(prof_env) != 0 && trials[0]->dtype == RFK_F16) {
     // development aid: synchronous, allocates; prints the per-role blocked-cycle breakdown
@@ -825,6 +847,14 @@ int fused_forward(rfk_mlp* const* trials, int w, int total_trials, const uint8_t
   else
     fused_ensemble_kernel<false, false><<<grid, kThreads, SMEM_BYTES, st>>>(P, x_map);
   RFK_LAUNCH_CHECK("fused_ensemble_kernel");
+  if (split) {
+    // kernel 3 over the W per-trial outputs: same float64 sum and rounding as the in-kernel mean
+    const float* ptrs[RFK_MAX_TRIALS];
+    for (int t = 0; t < w; ++t) ptrs[t] = static_cast<const float*>(ws) + (size_t)t * (size_t)n * P.n_classes;
+    int rc = rfk_ensemble_mean(ptrs, w, n, P.n_classes, out, st);
+    if (rc != RFK_OK) return rc;
+    if (total_trials != w) return scale_inplace(out, n * (int64_t)P.n_classes, (double)total_trials / (double)w, st);
+  }
   return RFK_OK;
 }
 

@@ -189,7 +189,7 @@ extern "C" int rfk_mlp_forward(rfk_mlp_t* h, const uint8_t* x, int64_t n, float*
   if (h->dtype == RFK_F32) return rfk::mlp_f32_forward(h, x, n, probs, workspace, workspace_bytes, st);
   if (h->fusable) {
     rfk_mlp* one[1] = {h};
-    return rfk::fused_forward(one, 1, 1, x, n, probs, st);
+    return rfk::fused_forward(one, 1, 1, x, n, probs, nullptr, 0, st);
   }
   return rfk::tc_forward(h, x, n, probs, workspace, workspace_bytes, st);
 }
@@ -212,7 +212,7 @@ extern "C" int rfk_ensemble_workspace_bytes(rfk_mlp_t* const* trials, int w, int
               "ensemble_workspace_bytes: bad argument");
   for (int t = 0; t < w; ++t) RFK_REQUIRE(trials[t] != nullptr, "ensemble_workspace_bytes: trials[%d] is NULL", t);
   if (all_fusable(trials, w)) {
-    *out = 0;
+    *out = rfk::fused_workspace_bytes(w, trials[0]->n_classes, n);
     return RFK_OK;
   }
   // unfused: one probs buffer per trial + the largest per-trial scratch (trials run in turn)
@@ -246,7 +246,8 @@ extern "C" int rfk_ensemble_forward(rfk_mlp_t* const* trials, int w, int total_t
   if (n == 0) return RFK_OK;
   RFK_REQUIRE(x != nullptr && out != nullptr, "ensemble_forward: NULL buffer");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  if (all_fusable(trials, w)) return rfk::fused_forward(trials, w, total_trials, x, n, out, st);
+  if (all_fusable(trials, w))
+    return rfk::fused_forward(trials, w, total_trials, x, n, out, workspace, workspace_bytes, st);
 
   size_t need = 0;
   int rc = rfk_ensemble_workspace_bytes(trials, w, n, &need);

@@ -21,8 +21,10 @@ bool fused_applicable(const rfk_mlp* h);
 int fused_prepare(rfk_mlp* h);
 void fused_release(rfk_mlp* h);
 // out = sum_w probs_w / total_trials over the w trials given (w == total_trials: the mean)
+// optional scratch of fused_workspace_bytes() enables the one-item-per-SM schedule for small batches
+size_t fused_workspace_bytes(int w, int n_classes, int64_t n);
 int fused_forward(rfk_mlp* const* trials, int w, int total_trials, const uint8_t* x, int64_t n,
-                  float* out, cudaStream_t st);
+                  float* out, void* ws, size_t ws_bytes, cudaStream_t st);
 
 // ensemble.cu
 int scale_inplace(float* p, int64_t count, double divisor, cudaStream_t st);

@@ -39,6 +39,19 @@ class DistributedEnsemble:
         self.world_size = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
 
+    def forward_async(self, x, out):
+        """Local kernel on the current stream, then the reduce as an asynchronous collective (NCCL
+        runs it on its own stream, ordered after the kernel).  Returns the work handle (``None``
+        for a single rank); ``out`` must not be reused before ``handle.wait()``.  With two ``out``
+        buffers used in turn the reduce of batch i overlaps the kernel of batch i+1."""
+        if self.local is not None:
+            self.local.forward(x, out=out)
+        else:
+            out.zero_()
+        if self.world_size > 1:
+            return dist.reduce(out, dst=self.root, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+        return None
+
     def forward(self, x, out=None):
         n = x.shape[0]
         if out is None:
