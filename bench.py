@@ -38,6 +38,9 @@ WORKLOADS = {
                name='8-trial TfFeedForward ensemble, 28x28, batch 65536 (BASELINE configs[2])'),
     'c2': dict(trials=3, batch=4096, image_size=28, channels=1, hidden=128, layers=2, scaling='weak',
                name='3-trial TfFeedForward ensemble, 28x28, batch 4096 per GPU (BASELINE configs[1])'),
+    'c4': dict(trials=1, batch=65536, image_size=32, channels=3, hidden=2048, layers=3, scaling='strong', shard='rows',
+               name='wide MLP trial (3x2048 hidden), 32x32x3 queries, batch 65536 sharded data-parallel '
+                    '(BASELINE configs[3])'),
     'c5': dict(trials=3, batch=65536, image_size=28, channels=1, hidden=128, layers=2, scaling='weak', sweep=True,
                name='serving latency sweep, batch 1..65536, 3-trial ensemble (BASELINE configs[4])'),
 }
@@ -223,9 +226,15 @@ def main():
         os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
         dist.init_process_group('nccl', device_id=dev)
 
-    params, batches, d = make_workload(wl)
+    params, batches, d = make_workload(wl, n_batches=2 if wl.get('shard') == 'rows' else None)
     n, W, C = wl['batch'], wl['trials'], synth.NUM_CLASSES
-    if wl['scaling'] == 'strong':      # trials dealt round-robin to ranks; every rank sees the whole batch
+    n_total = n
+    if wl.get('shard') == 'rows':      # one trial, rows of the batch split over ranks, no collective
+        mine = list(range(W))
+        lo, hi = rank * n // world, (rank + 1) * n // world
+        batches = [np.ascontiguousarray(b[lo:hi]) for b in batches]
+        n = hi - lo
+    elif wl['scaling'] == 'strong':    # trials dealt round-robin to ranks; every rank sees the whole batch
         mine = [t for t in range(W) if t % world == rank]
     else:                              # independent replicas
         mine = list(range(W))
@@ -234,7 +243,7 @@ def main():
     ens = engine.Ensemble(trials, total_trials=W) if trials else None
     xs = [torch.from_numpy(b).to(dev) for b in batches]
     out = torch.zeros((n, C), dtype=torch.float32, device=dev)
-    do_reduce = world > 1 and wl['scaling'] == 'strong'
+    do_reduce = world > 1 and wl['scaling'] == 'strong' and wl.get('shard') != 'rows'
     dens = DistributedEnsemble(ens, W, C, dev, root=0) if do_reduce else None
 
     outs = [out, torch.zeros_like(out)]
@@ -284,7 +293,7 @@ def main():
         t = torch.tensor([ms], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
-    units = n * args.steps * (world if wl['scaling'] == 'weak' else 1)
+    units = (n_total if wl.get('shard') == 'rows' else n) * args.steps * (world if wl['scaling'] == 'weak' else 1)
     value = units / (ms * 1e-3)
 
     # ---- per-batch latency (the metric's "p99 batch latency"): one step at a time, device timed
@@ -352,7 +361,7 @@ def main():
             t = torch.tensor([dt], device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             dt = float(t.item())
-        e_units = n * e2e_steps * (world if wl['scaling'] == 'weak' else 1)
+        e_units = (n_total if wl.get('shard') == 'rows' else n) * e2e_steps * (world if wl['scaling'] == 'weak' else 1)
         e2e = {'value': e_units / dt, 'unit': 'queries/s', 'h2d_bytes_per_step': pipe.h2d_bytes,
                'd2h_bytes_per_step': pipe.d2h_bytes, 'steps': e2e_steps, 'slots_in_flight': depth,
                'note': 'per rank: H2D of the whole uint8 batch + fused kernel + D2H of the probabilities'}
@@ -380,16 +389,19 @@ def main():
             'config': {'workload': wl['name'], 'trials': W, 'batch': n, 'd': d, 'hidden_units': wl['hidden'],
                        'hidden_layers': wl['layers'], 'classes': C,
                        'parallelism': ('trial-per-gpu x{} + nccl reduce'.format(world) if do_reduce else
-                                       ('replicas x{}'.format(world) if world > 1 else 'single gpu, fused ensemble')),
+                                       ('rows sharded x{}'.format(world) if wl.get('shard') == 'rows' else
+                                        ('replicas x{}'.format(world) if world > 1 else 'single gpu, fused ensemble'))),
                        'l2': 'rotating over {} distinct resident batches ({} MB > L2)'.format(
                            len(xs), len(xs) * n * d // (1 << 20))},
             'clocks': clocks,
             'latency': latency,
             'e2e': e2e,
-            'gpu_launches': args.steps * (1 if ens is not None else 0),
+            'gpu_launches': args.steps * ((len(params[0]['kernels']) + 1) if wl.get('shard') == 'rows' else (1 if ens is not None else 0)),
             'roofline': {'bound': 'tensor', 'achieved': achieved, 'peak': peak, 'unit': 'TFLOP/s',
                          'frac': achieved / peak, 'traffic': traffic,
-                         'kernel': 'fused_ensemble_kernel (one launch per step; duration = timed region / steps)',
+                         'kernel': ('gemm_bias_act_kernel x4 + decode (whole step; duration = timed region / steps)'
+                                    if wl.get('shard') == 'rows' else
+                                    'fused_ensemble_kernel (one launch per step; duration = timed region / steps)'),
                          'peak_source': peaks['_source'] + ', bf16_tflops_sustained (same rate for fp16)',
                          'flops_per_launch': flops_per_launch,
                          'hbm_gbs_algorithmic': n * (d + 4 * C) / (ms_launch * 1e-3) / 1e9},

@@ -8,6 +8,8 @@
 // Design: persistent CTAs (a multiple of the SM count), the per-feature scale/shift
 // vectors staged once per CTA in shared memory, one 16-byte load (16 pixels) per thread
 // per step, 16-byte stores, streaming cache hints on both sides.
+#include <type_traits>
+
 #include "rfk_common.cuh"
 
 namespace {
@@ -32,6 +34,15 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
   return r;
 }
+__device__ __forceinline__ uint32_t pack_f16(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+template <typename Out>
+__device__ __forceinline__ uint32_t pack16(float lo, float hi) {
+  return sizeof(Out) == 2 && !std::is_same<Out, __nv_bfloat16>::value ? pack_f16(lo, hi) : pack_bf16(lo, hi);
+}
 __device__ __forceinline__ float byte_to_float(uint32_t word, int i) {
   return (float)((word >> (8 * i)) & 0xffu);
 }
@@ -43,6 +54,10 @@ __device__ __forceinline__ void store_one<float>(float* p, float v) { *p = v; }
 template <>
 __device__ __forceinline__ void store_one<__nv_bfloat16>(__nv_bfloat16* p, float v) {
   *p = __float2bfloat16_rn(v);
+}
+template <>
+__device__ __forceinline__ void store_one<__half>(__half* p, float v) {
+  *p = __float2half_rn(v);
 }
 
 // Fast path: d % 16 == 0, ld_out == d, 16-byte aligned pointers.  One thread = 16 pixels of
@@ -86,10 +101,10 @@ decode_vec16_kernel(const uint8_t* __restrict__ x, Out* __restrict__ y, int64_t 
     }
     if (sizeof(Out) == 2) {
       uint4 o0, o1;
-      o0.x = pack_bf16(v[0], v[1]);   o0.y = pack_bf16(v[2], v[3]);
-      o0.z = pack_bf16(v[4], v[5]);   o0.w = pack_bf16(v[6], v[7]);
-      o1.x = pack_bf16(v[8], v[9]);   o1.y = pack_bf16(v[10], v[11]);
-      o1.z = pack_bf16(v[12], v[13]); o1.w = pack_bf16(v[14], v[15]);
+      o0.x = pack16<Out>(v[0], v[1]);   o0.y = pack16<Out>(v[2], v[3]);
+      o0.z = pack16<Out>(v[4], v[5]);   o0.w = pack16<Out>(v[6], v[7]);
+      o1.x = pack16<Out>(v[8], v[9]);   o1.y = pack16<Out>(v[10], v[11]);
+      o1.z = pack16<Out>(v[12], v[13]); o1.w = pack16<Out>(v[14], v[15]);
       char* dst = reinterpret_cast<char*>(y) + c * 32;
       st_stream_16(dst, o0);
       st_stream_16(dst + 16, o1);
@@ -205,6 +220,8 @@ int decode_dispatch(const uint8_t* x, void* y, int64_t n, int d, int ld_out, con
     return launch_decode<float>(x, static_cast<float*>(y), n, d, ld_out, scale, shift, s_in, s_out, ch, st);
   if (out_dtype == RFK_BF16)
     return launch_decode<__nv_bfloat16>(x, static_cast<__nv_bfloat16*>(y), n, d, ld_out, scale, shift, s_in, s_out, ch, st);
+  if (out_dtype == RFK_F16)
+    return launch_decode<__half>(x, static_cast<__half*>(y), n, d, ld_out, scale, shift, s_in, s_out, ch, st);
   rfk::set_error("decode: unknown out_dtype %d", out_dtype);
   return RFK_ERR_INVALID;
 }

@@ -42,4 +42,26 @@ int make_tmap_u8_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t 
   return RFK_OK;
 }
 
+int make_tmap_16bit_sw128(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t pitch_bytes,
+                          uint32_t box_rows) {
+  EncodeTiledFn fn = encoder();
+  if (fn == nullptr) {
+    set_error("cuTensorMapEncodeTiled is not available from this driver");
+    return RFK_ERR_CUDA;
+  }
+  const cuuint64_t dims[2] = {cols, rows};
+  const cuuint64_t strides[1] = {pitch_bytes};
+  const cuuint32_t box[2] = {64, box_rows};
+  const cuuint32_t elem[2] = {1, 1};
+  const CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, const_cast<void*>(base), dims, strides, box, elem,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled(16-bit) failed with CUresult %d (base %p rows %llu cols %llu pitch %llu)", (int)r,
+              base, (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)pitch_bytes);
+    return RFK_ERR_CUDA;
+  }
+  return RFK_OK;
+}
+
 }  // namespace rfk

@@ -12,4 +12,9 @@ namespace rfk {
 int make_tmap_u8_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t pitch,
                     uint32_t box_rows, uint32_t box_cols);
 
+// 2-D row-major tensor of 16-bit elements [rows, cols] with row pitch `pitch_bytes`; box = box_rows x
+// 64 elements (128 bytes) written to shared memory with the 128-byte swizzle tcgen05.mma expects.
+int make_tmap_16bit_sw128(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t pitch_bytes,
+                          uint32_t box_rows);
+
 }  // namespace rfk

@@ -281,3 +281,30 @@ def test_errors_are_reported_not_swallowed():
     bad['kernels'] = [params['kernels'][0]] + [np.zeros((9, 10), np.float32)]
     with pytest.raises(ValueError):
         engine.Trial(bad)
+
+
+# ------------------------------------------------------------------------------- wide trials (layered tcgen05 GEMMs)
+@pytest.mark.parametrize('S,ch,L,H,n', [(32, 3, 3, 2048, 300), (28, 1, 2, 300, 517), (32, 3, 1, 256, 129),
+                                        (28, 1, 3, 64, 64)])
+@pytest.mark.parametrize('compute,tol', [('f16', TOL_TC), ('bf16', TOL_BF16), ('f32', TOL_F32)])
+def test_wide_trial_layered_path(S, ch, L, H, n, compute, tol):
+    """BASELINE config 4 shape (D 3072, 3 x 2048) and other trials the fused kernel does not take."""
+    params, X = _case(S, ch, L, H, n)
+    tr = engine.Trial(params, compute=compute)
+    assert not tr.fused
+    got = _np(tr.forward(torch.from_numpy(X).cuda()))
+    want = ff.forward(params, X, np.float32)
+    assert np.isfinite(got).all()
+    assert np.abs(got - want).max() <= tol
+    assert np.abs(got.sum(1) - 1).max() <= 1e-5
+    tr.close()
+
+
+def test_wide_trial_in_an_ensemble_with_a_fused_one():
+    dead = synth.dead_mask(784)
+    params = [synth.make_trial(0, 28, 1, 2, 300, dead=dead), synth.make_trial(1, 28, 1, 2, 64, dead=dead)]
+    X = synth.make_queries(700, 28, 1, 'uniform', seed=4, dead=dead)
+    trials = [engine.Trial(p) for p in params]
+    got = engine.Ensemble(trials).forward(torch.from_numpy(X).cuda()).cpu().numpy()
+    want = ff.ensemble_mean_array([ff.forward(p, X, np.float32) for p in params])
+    assert np.abs(got.astype(np.float64) - want).max() <= TOL_TC
