@@ -378,7 +378,7 @@ def main():
         summ = os.path.join(ROOT, 'profiles', 'ncu_summary.json')
         if os.path.exists(summ):
             try:
-                traffic = json.load(open(summ)).get(args.workload, {}).get('fused_dram_bytes_per_launch')
+                traffic = json.load(open(summ)).get(args.workload, {}).get('fused_dram_bytes_per_launch') if world == 1 else None
             except Exception:
                 traffic = None
         line = {
