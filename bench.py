@@ -203,6 +203,8 @@ def main():
     ap.add_argument('--workload', default='c3', choices=sorted(WORKLOADS))
     ap.add_argument('--compute', default='f16', choices=['f16', 'bf16', 'f32'])
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--reduce', default='peer', choices=['peer', 'nccl'],
+                    help='N > 1, trial-per-GPU workloads: fused peer-memory reduce (default) or torch.distributed/NCCL')
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
     if args.impl == 'reference':
@@ -245,12 +247,19 @@ def main():
     out = torch.zeros((n, C), dtype=torch.float32, device=dev)
     do_reduce = world > 1 and wl['scaling'] == 'strong' and wl.get('shard') != 'rows'
     dens = DistributedEnsemble(ens, W, C, dev, root=0) if do_reduce else None
+    reducer = None
+    if do_reduce and args.reduce == 'peer':
+        from rafiki_b200.distributed import PeerReducer
+        reducer = PeerReducer(n, C, dev, root=0)
 
     outs = [out, torch.zeros_like(out)]
     pending = [None, None]
 
     def step(i):
-        if dens is not None:
+        if reducer is not None:
+            # local fused kernel, then kernel 3 fused with the collective over NVLink peer memory
+            dens.forward_peer(xs[i % len(xs)], reducer)
+        elif dens is not None:
             # local fused kernel + NCCL reduce onto rank 0; two result buffers in turn, so the
             # reduce of batch i overlaps the kernel of batch i+1
             slot = i & 1
@@ -323,9 +332,9 @@ def main():
                 barrier()
                 t0 = time.perf_counter()
             d_in.copy_(h_in, non_blocking=True)
-            dens.forward(d_in, out=out)
+            res = dens.forward_peer(d_in, reducer) if reducer is not None else dens.forward(d_in, out=out)
             if rank == 0:
-                h_out.copy_(out, non_blocking=True)
+                h_out.copy_(res, non_blocking=True)
         barrier()
         dt = time.perf_counter() - t0
         t = torch.tensor([dt], device=dev)
@@ -388,7 +397,9 @@ def main():
             'data': 'synthetic',
             'config': {'workload': wl['name'], 'trials': W, 'batch': n, 'd': d, 'hidden_units': wl['hidden'],
                        'hidden_layers': wl['layers'], 'classes': C,
-                       'parallelism': ('trial-per-gpu x{} + nccl reduce'.format(world) if do_reduce else
+                       'parallelism': ('trial-per-gpu x{} + {}'.format(world, 'fused peer-memory reduce (NVLink)' if
+                                                                       reducer is not None else 'nccl reduce')
+                                       if do_reduce else
                                        ('rows sharded x{}'.format(world) if wl.get('shard') == 'rows' else
                                         ('replicas x{}'.format(world) if world > 1 else 'single gpu, fused ensemble'))),
                        'l2': 'rotating over {} distinct resident batches ({} MB > L2)'.format(
@@ -396,7 +407,8 @@ def main():
             'clocks': clocks,
             'latency': latency,
             'e2e': e2e,
-            'gpu_launches': args.steps * ((len(params[0]['kernels']) + 1) if wl.get('shard') == 'rows' else (1 if ens is not None else 0)),
+            'gpu_launches': args.steps * ((len(params[0]['kernels']) + 1) if wl.get('shard') == 'rows' else
+                                          ((1 if ens is not None else 0) + (2 if reducer is not None else 0))),
             'roofline': {'bound': 'tensor', 'achieved': achieved, 'peak': peak, 'unit': 'TFLOP/s',
                          'frac': achieved / peak, 'traffic': traffic,
                          'kernel': ('gemm_bias_act_kernel x4 + decode (whole step; duration = timed region / steps)'

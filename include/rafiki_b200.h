@@ -144,6 +144,24 @@ int rfk_ensemble_forward(rfk_mlp_t* const* trials, int w, int total_trials, cons
                          int64_t n, float* out, void* workspace, size_t workspace_bytes,
                          void* stream);
 
+/*
+ * Kernel 3 across the GPUs of one box: the mean over ranks fused with the collective.
+ * Replaces: the Predictor's gather of one answer per worker + ensemble_predictions
+ * (rafiki/predictor/predictor.py:46-70, rafiki/predictor/ensemble.py:10-14) for
+ * one-process-per-GPU ranks.  probs[j] / flags[j]: rank j's partial-mean buffer (count floats,
+ * as written by rfk_ensemble_forward with total_trials = all trials) and flag block
+ * (2 * world + 1 zero-initialised uint32), mapped into this process (CUDA IPC); HOST arrays of
+ * `world` DEVICE pointers.  Every rank calls rfk_peer_reduce with the same step (1, 2, ...),
+ * count and grid_blocks; rank r sums slice r of the elements over all ranks (float64, rank
+ * order, one rounding) and stores it into root_out, the ROOT's result buffer.  The root then
+ * calls rfk_peer_wait on its own flag block; after it, root_out holds the full mean.
+ * Callers alternate two probs / result buffers by step parity.
+ */
+int rfk_peer_reduce(const float* const* probs, unsigned int* const* flags, int world, int rank,
+                    int root, unsigned int step, int64_t count, float* root_out, int grid_blocks,
+                    void* stream);
+int rfk_peer_wait(const unsigned int* flags_of_this_rank, int world, unsigned int step, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

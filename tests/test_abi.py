@@ -52,3 +52,11 @@ def test_missing_library_fails_loudly(monkeypatch, tmp_path):
     monkeypatch.setattr(_native, 'LIB_PATH', str(tmp_path / 'nope.so'))
     with pytest.raises(ImportError, match='no CPU fallback'):
         _native.load()
+
+
+def test_peer_reduce_argument_validation():
+    lib = _native.load()
+    assert lib.rfk_peer_reduce(None, None, 2, 0, 0, 1, 8, None, 4, None) == 1
+    assert lib.rfk_peer_reduce(None, None, 99, 0, 0, 1, 8, None, 4, None) == 1
+    assert b'world' in lib.rfk_last_error()
+    assert lib.rfk_peer_wait(None, 2, 1, None) == 1

@@ -308,3 +308,18 @@ def test_wide_trial_in_an_ensemble_with_a_fused_one():
     got = engine.Ensemble(trials).forward(torch.from_numpy(X).cuda()).cpu().numpy()
     want = ff.ensemble_mean_array([ff.forward(p, X, np.float32) for p in params])
     assert np.abs(got.astype(np.float64) - want).max() <= TOL_TC
+
+
+def test_mixed_ensemble_with_an_external_plugin():
+    """ensembles can mix model classes (examples/scripts/quickstart.py:78-82 trains
+    TfFeedForward + SkDt); kernel 3 takes any [n, C] probability block, e.g. one uploaded from a
+    CPU plugin's predict_proba."""
+    params, X = _case(28, 1, 2, 64, 777)
+    tr = engine.Trial(params)
+    gpu_probs = tr.forward(torch.from_numpy(X).cuda())
+    rng = np.random.default_rng(1)
+    tree = rng.dirichlet(np.ones(10), size=777).astype(np.float32)          # a decision tree's predict_proba
+    got = engine.ensemble_mean([gpu_probs, torch.from_numpy(tree).cuda()]).cpu().numpy()
+    want = ff.ensemble_predictions([gpu_probs.cpu().numpy().tolist(), tree.tolist()], 'IMAGE_CLASSIFICATION')
+    assert np.array_equal(got, np.asarray(want).astype(np.float32))
+    tr.close()
