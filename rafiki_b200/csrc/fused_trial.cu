@@ -51,13 +51,16 @@ namespace {
 using namespace sm100;
 
 constexpr int TILE_M = 128;
-constexpr int KB = 64;          // K elements per pipeline step (one 128-byte swizzle atom of 16-bit operands)
-constexpr int STAGES = 3;       // A / B operand ring
-constexpr int RAW_STAGES = 4;   // raw uint8 ring (TMA landing zone; covers HBM latency)
+constexpr int ATOM_K = 64;      // K elements of one 128-byte swizzle atom of 16-bit operands
+constexpr int KB = 128;         // K elements per pipeline step: two atoms, so that every barrier round
+                                // (loader -> converter -> MMA issuer) carries eight MMAs instead of four
+constexpr int STAGES = 2;       // A / B operand ring
+constexpr int RAW_STAGES = 3;   // raw uint8 ring (TMA landing zone; covers HBM latency)
 constexpr int HMAX = 128;       // widest hidden layer the fused path takes
 constexpr int CPAD = 16;        // class dimension padded to one UMMA N step
-constexpr int A_STAGE = TILE_M * 128;
-constexpr int B_STAGE = HMAX * 128;
+constexpr int A_ATOM = TILE_M * 128;              // one 64-wide atom of the A tile
+constexpr int A_STAGE = (KB / ATOM_K) * A_ATOM;
+constexpr int B_STAGE = (KB / ATOM_K) * HMAX * 128;
 constexpr int RAW_STAGE = TILE_M * KB;            // 8192 bytes of uint8
 constexpr int W2_BYTES = 2 * HMAX * 128;
 constexpr int W3_BYTES = 2 * CPAD * 128;
@@ -83,8 +86,8 @@ static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
 // the light roles give registers back and the epilogue warps take them.
 constexpr int kEpiWarps = 8, kConvWarps = 8;
 constexpr int kEpiThreads = kEpiWarps * 32;                   // 256
-constexpr int kConvThreads = kConvWarps * 32;                 // 256: two 16-byte pieces per thread per step
-constexpr int kConvPieces = (TILE_M * KB / 16) / kConvThreads;   // 2
+constexpr int kConvThreads = kConvWarps * 32;                 // 256: four 16-byte pieces per thread per step
+constexpr int kConvPieces = (TILE_M * KB / 16) / kConvThreads;   // 4
 constexpr int kThreads = (kEpiWarps + kConvWarps + 4) * 32;   // 640
 constexpr int WARP_LOAD = kEpiWarps + kConvWarps, WARP_MMA = WARP_LOAD + 1, WARP_PAR = WARP_LOAD + 2,
               WARP_TAIL = WARP_LOAD + 3;
@@ -183,7 +186,8 @@ __device__ __forceinline__ void hidden_store16(const uint32_t (&v)[16], int c, c
 
 // Columns [c_begin, c_end) of one TMEM accumulator row -> hidden activations (A operand of the
 // next layer, kept in tensor memory).  16 columns per step; the TMEM load of step s+1 is in flight
-// while step s is converted and stored (two statically named buffers: everything stays in registers).
+// while step s is converted and stored (two statically named buffers: everything stays in registers;
+// four buffers were measured to spill under the 96-register launch bound).
 template <bool kF16>
 __device__ __forceinline__ void epilogue_hidden(uint32_t tmem_row_addr, int c_begin, int c_end, const float* bias,
                                                 uint32_t hid_row_addr) {
@@ -421,14 +425,15 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
     // offsets are fixed per thread, so a step is 2 x (LDS.128, 16 conversions, 2 x STS.128).
     asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsLight));
     const int tp = threadIdx.x - kEpiThreads;                    // 0..255
-    const int q = tp & 3;
-    const int r0 = tp >> 2;                                      // 0..63
+    const int q = tp & 7;                                        // 16-byte piece of the 128-byte raw row
+    const int r0 = tp >> 3;                                      // 0..31
     const uint32_t sw = (uint32_t)(r0 & 7);
     const uint32_t raw_off = smem_base + OFF_RAW + (uint32_t)r0 * KB + (uint32_t)q * 16u;
-    const uint32_t a_off_lo = smem_base + OFF_A + (uint32_t)r0 * 128u + ((((uint32_t)(2 * q)) ^ sw) << 4);
-    const uint32_t a_off_hi = smem_base + OFF_A + (uint32_t)r0 * 128u + ((((uint32_t)(2 * q + 1)) ^ sw) << 4);
-    const int last_cols = P.d - (n_kb - 1) * KB;                 // valid bytes per row in the ragged last block
-    constexpr uint32_t kRowsPerPass = TILE_M / kConvPieces;      // 64
+    // piece q covers K elements 16q..16q+15 of the step: atom q / 4, 16-byte chunks 2(q%4), 2(q%4)+1
+    const uint32_t a_row = smem_base + OFF_A + (uint32_t)(q >> 2) * A_ATOM + (uint32_t)r0 * 128u;
+    const uint32_t a_off_lo = a_row + ((((uint32_t)(2 * (q & 3))) ^ sw) << 4);
+    const uint32_t a_off_hi = a_row + ((((uint32_t)(2 * (q & 3) + 1)) ^ sw) << 4);
+    constexpr uint32_t kRowsPerPass = TILE_M / kConvPieces;      // 32
     int stage = 0, rstage = 0;
     uint32_t phase = 0, rphase = 0;
     // the probes of step s+1's barriers are issued while step s is converted
@@ -436,12 +441,10 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
     for (int tile = tile0; tile < P.n_tiles; tile += tile_step) {
       for (int t = t0; t < t1; ++t) {
         for (int kb = 0; kb < n_kb; ++kb) {
-          if (!raw_ready) wait_prof<kProf>(&bars->raw_full[rstage], rphase, prof, PF_CONV_RAW);
-          if (warp == kEpiWarps) RFK_TRACE(0, 1);
-          if (!slot_ready) wait_prof<kProf>(&bars->empty[stage], phase ^ 1u, prof, PF_CONV_EMPTY);
-          if (warp == kEpiWarps) RFK_TRACE(0, 2);
+          if (!raw_ready) mbar_wait(&bars->raw_full[rstage], rphase);
+          if (!slot_ready) mbar_wait(&bars->empty[stage], phase ^ 1u);
           // columns past the end of the row are never read by the MMAs: skip their conversion
-          const bool live = !(P.debug & 2) && (kb < n_kb - 1 || q * 16 < last_cols);
+          const bool live = !(P.debug & 2) && (kb * KB + q * 16 < P.d);
           if (!live) raw_ready = slot_ready = false;
           if (live) {
             const uint32_t rsrc = raw_off + (uint32_t)rstage * RAW_STAGE;
@@ -515,9 +518,11 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
     for (int tile = tile0; tile < P.n_tiles; tile += tile_step) {
       for (int t = t0; t < t1; ++t) {
         const TrialDev& T = P.trial[t];
-        const uint32_t bytes = (uint32_t)T.h1_pad * 128u;
+        const uint32_t atom_bytes = (uint32_t)T.h1_pad * 128u;        // one 64-wide K atom of W1
+        const int n_atoms = (P.d + ATOM_K - 1) / ATOM_K;
         const uint8_t* src = T.w1;
         for (int kb = 0; kb < n_kb; ++kb) {
+          const uint32_t bytes = atom_bytes * (uint32_t)(n_atoms - 2 * kb < 2 ? n_atoms - 2 * kb : 2);
           if (r_step < total_steps) issue_raw();
           wait_prof<kProf>(&bars->empty[stage], phase ^ 1u, prof, PF_LOAD_EMPTY);
           RFK_TRACE(1, 3);
@@ -526,7 +531,7 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
               mbar_arrive(&bars->full[stage]);
             } else {
               mbar_arrive_expect_tx(&bars->full[stage], bytes);
-              bulk_g2s(smem + OFF_B + stage * B_STAGE, src + (size_t)kb * bytes, bytes, &bars->full[stage]);
+              bulk_g2s(smem + OFF_B + stage * B_STAGE, src + (size_t)kb * 2 * atom_bytes, bytes, &bars->full[stage]);
             }
           }
           __syncwarp();
@@ -584,7 +589,6 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
     int stage = 0;
     uint32_t phase = 0;
     const uint32_t a_lo0 = desc_lo_sw128(smem_base + OFF_A), b_lo0 = desc_lo_sw128(smem_base + OFF_B);
-    const int last_ksteps = (P.d - (n_kb - 1) * KB) >> 4;      // K steps of the ragged last block (1..4)
     bool next_ready = false;
     int item = 0;
     for (int tile = tile0; tile < P.n_tiles; tile += tile_step) {
@@ -599,11 +603,15 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
           if (!next_ready) wait_prof<kProf>(&bars->full[stage], phase, prof, PF_MMA_FULL);
           RFK_TRACE(2, 1);
           tc_fence_after_sync();
-          const int ksteps = kb == n_kb - 1 ? last_ksteps : 4;
           if (!(P.debug & 4)) {
+            // two 64-wide atoms per step; the ragged end of the row may leave the second one short or empty
+            const int k16 = (P.d - kb * KB) >> 4;                      // 16-element K steps left in this row
             const uint32_t a = a_lo0 + (uint32_t)stage * (A_STAGE >> 4);
             const uint32_t b = b_lo0 + (uint32_t)stage * (B_STAGE >> 4);
-            mma4_f16_ss_elect(d_tmem, desc_from_lo(a), desc_from_lo(b), idesc1, kb != 0, ksteps);
+            mma4_f16_ss_elect(d_tmem, desc_from_lo(a), desc_from_lo(b), idesc1, kb != 0, k16 < 4 ? k16 : 4);
+            if (k16 > 4)
+              mma4_f16_ss_elect(d_tmem, desc_from_lo(a + (A_ATOM >> 4)), desc_from_lo(b + (((uint32_t)T.h1_pad * 128u) >> 4)),
+                                idesc1, 1u, k16 - 4 < 4 ? k16 - 4 : 4);
           }
           RFK_TRACE(2, 2);
           const int cur = stage;
