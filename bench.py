@@ -270,6 +270,9 @@ def main():
             ens.forward(xs[i % len(xs)], out=out)
 
     def drain():
+        if reducer is not None:
+            reducer.wait(0)
+            reducer.wait(1)
         for k in range(2):
             if pending[k] is not None:
                 pending[k].wait()
@@ -333,6 +336,8 @@ def main():
                 t0 = time.perf_counter()
             d_in.copy_(h_in, non_blocking=True)
             res = dens.forward_peer(d_in, reducer) if reducer is not None else dens.forward(d_in, out=out)
+            if reducer is not None:
+                reducer.wait()
             if rank == 0:
                 h_out.copy_(res, non_blocking=True)
         barrier()

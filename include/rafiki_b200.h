@@ -157,6 +157,15 @@ int rfk_ensemble_forward(rfk_mlp_t* const* trials, int w, int total_trials, cons
  * calls rfk_peer_wait on its own flag block; after it, root_out holds the full mean.
  * Callers alternate two probs / result buffers by step parity.
  */
+/* Set-up of the peer path: rfk_peer_alloc makes one zero-filled device block other processes of the
+ * box can map (handle64: 64 bytes to send them); rfk_peer_open maps such a block for kernels of the
+ * current device; rfk_peer_close / rfk_peer_free undo them.  Set-up only: they allocate and synchronise. */
+int rfk_peer_alloc(size_t bytes, void** dptr, void* handle64);
+int rfk_peer_open(const void* handle64, void** dptr);
+int rfk_peer_close(void* dptr);
+int rfk_peer_free(void* dptr);
+/* Let kernels on the current device load/store the memory of `peer_device` (once per pair). */
+int rfk_peer_enable(int peer_device);
 int rfk_peer_reduce(const float* const* probs, unsigned int* const* flags, int world, int rank,
                     int root, unsigned int step, int64_t count, float* root_out, int grid_blocks,
                     void* stream);

@@ -48,6 +48,11 @@ PROTOTYPES = {
     'rfk_ensemble_mean': (_i, [_c.POINTER(_vp), _i, _i64, _i, _vp, _vp]),
     'rfk_ensemble_workspace_bytes': (_i, [_c.POINTER(_vp), _i, _i64, _c.POINTER(_sz)]),
     'rfk_ensemble_forward': (_i, [_c.POINTER(_vp), _i, _i, _vp, _i64, _vp, _vp, _sz, _vp]),
+    'rfk_peer_alloc': (_i, [_sz, _c.POINTER(_vp), _vp]),
+    'rfk_peer_open': (_i, [_vp, _c.POINTER(_vp)]),
+    'rfk_peer_close': (_i, [_vp]),
+    'rfk_peer_free': (_i, [_vp]),
+    'rfk_peer_enable': (_i, [_i]),
     'rfk_peer_reduce': (_i, [_c.POINTER(_vp), _c.POINTER(_vp), _i, _i, _i, _c.c_uint, _i64, _vp, _i, _vp]),
     'rfk_peer_wait': (_i, [_vp, _i, _c.c_uint, _vp]),
 }

@@ -18,6 +18,8 @@
 // Flags are monotonic step counters, so nothing is ever reset; buffers are double buffered by
 // step parity by the caller (rafiki_b200/distributed.py).  Every spin is bounded: a rank that
 // died makes the others trap after ~2 s instead of hanging the box.
+#include <string.h>
+
 #include "rfk_internal.cuh"
 
 namespace {
@@ -45,9 +47,12 @@ __device__ __forceinline__ bool spin_until_ge(const unsigned int* p, unsigned in
   }
   return true;
 }
+// The partials were complete before their owner raised its flag (acquired above) and do not change
+// while this kernel runs, so the loads may be hoisted and overlapped freely (non-coherent path;
+// the L1 is invalidated at every kernel launch, so nothing stale survives from the step before).
 __device__ __forceinline__ float4 ld_peer_f4(const float* p) {
   float4 r;
-  asm volatile("ld.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p) : "memory");
+  asm("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
   return r;
 }
 
@@ -73,10 +78,16 @@ peer_reduce_kernel(const PeerPtrs ptrs, int world, int rank, int root, unsigned 
   const long long stride = (long long)gridDim.x * kThreads;
   for (long long i = lo + (long long)blockIdx.x * kThreads + threadIdx.x; i < hi; i += stride) {
     double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
-    for (int j = 0; j < world; ++j) {
-      const float4 v = ld_peer_f4(ptrs.probs[j] + 4 * i);
-      s0 += (double)v.x; s1 += (double)v.y; s2 += (double)v.z; s3 += (double)v.w;
-    }
+    // all ranks' loads are issued before the first sum: NVLink latency is paid once per element
+    float4 v[kMaxRanks];
+#pragma unroll
+    for (int j = 0; j < kMaxRanks; ++j)
+      if (j < world) v[j] = ld_peer_f4(ptrs.probs[j] + 4 * i);
+#pragma unroll
+    for (int j = 0; j < kMaxRanks; ++j)
+      if (j < world) {
+        s0 += (double)v[j].x; s1 += (double)v[j].y; s2 += (double)v[j].z; s3 += (double)v[j].w;
+      }
     float4 o;
     o.x = (float)s0; o.y = (float)s1; o.z = (float)s2; o.w = (float)s3;
     *reinterpret_cast<float4*>(root_out + 4 * i) = o;
@@ -104,6 +115,61 @@ __global__ void peer_wait_kernel(const unsigned int* done_flags, int world, unsi
 }
 
 }  // namespace
+
+// One device allocation that other processes on the box can map: cudaMalloc + IPC handle (64 bytes).
+// Set-up-time calls (they allocate and synchronise); the data path above allocates nothing.
+extern "C" int rfk_peer_alloc(size_t bytes, void** dptr, void* handle64) {
+  RFK_REQUIRE(bytes > 0 && dptr != nullptr && handle64 != nullptr, "peer_alloc: bad argument");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  void* p = nullptr;
+  RFK_CUDA_TRY(cudaMalloc(&p, bytes));
+  RFK_CUDA_TRY(cudaMemset(p, 0, bytes));
+  RFK_CUDA_TRY(cudaDeviceSynchronize());
+  cudaIpcMemHandle_t h;
+  const cudaError_t e = cudaIpcGetMemHandle(&h, p);
+  if (e != cudaSuccess) {
+    cudaFree(p);
+    RFK_CUDA_TRY(e);
+  }
+  memcpy(handle64, &h, 64);
+  *dptr = p;
+  return RFK_OK;
+}
+// Map another process's rfk_peer_alloc block into this process, for kernels of the CURRENT device.
+extern "C" int rfk_peer_open(const void* handle64, void** dptr) {
+  RFK_REQUIRE(handle64 != nullptr && dptr != nullptr, "peer_open: bad argument");
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, 64);
+  RFK_CUDA_TRY(cudaIpcOpenMemHandle(dptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return RFK_OK;
+}
+extern "C" int rfk_peer_close(void* dptr) {
+  if (dptr != nullptr) RFK_CUDA_TRY(cudaIpcCloseMemHandle(dptr));
+  return RFK_OK;
+}
+extern "C" int rfk_peer_free(void* dptr) {
+  if (dptr != nullptr) RFK_CUDA_TRY(cudaFree(dptr));
+  return RFK_OK;
+}
+
+extern "C" int rfk_peer_enable(int peer_device) {
+  int dev = 0;
+  RFK_CUDA_TRY(cudaGetDevice(&dev));
+  if (peer_device == dev) return RFK_OK;
+  int can = 0;
+  RFK_CUDA_TRY(cudaDeviceCanAccessPeer(&can, dev, peer_device));
+  if (!can) {
+    rfk::set_error("peer_enable: device %d cannot map the memory of device %d (no NVLink / P2P path)", dev, peer_device);
+    return RFK_ERR_COMM;
+  }
+  const cudaError_t e = cudaDeviceEnablePeerAccess(peer_device, 0);
+  if (e == cudaErrorPeerAccessAlreadyEnabled) {
+    cudaGetLastError();   // clear the sticky-free error state
+    return RFK_OK;
+  }
+  RFK_CUDA_TRY(e);
+  return RFK_OK;
+}
 
 extern "C" int rfk_peer_reduce(const float* const* probs, unsigned int* const* flags, int world, int rank, int root,
                                unsigned int step, int64_t count, float* root_out, int grid_blocks, void* stream) {

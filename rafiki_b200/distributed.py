@@ -27,15 +27,14 @@ class PeerReducer:
     """Cross-rank mean over NVLink peer memory (``rfk_peer_reduce``): the collective fused into
     kernel 3 instead of an NCCL reduce.
 
-    Every rank owns two partial-mean buffers (alternating by step), two result buffers and one
-    flag block; the buffers are exported with CUDA IPC (through ``torch.multiprocessing``'s tensor
-    reduction) and opened by every other rank, so a kernel on GPU r can load rank j's partials and
-    store into the root's result directly.  ``reduce(step_buffer)`` enqueues, on the current stream:
+    Every rank owns one device block (``rfk_peer_alloc``) holding two partial-mean buffers
+    (alternating by step), two result buffers and a flag block; its CUDA IPC handle goes to every
+    other rank, which maps it with its own device current (``rfk_peer_open``), so a kernel on GPU r
+    can load rank j's partials and store into the root's result directly.  ``reduce(step_buffer)`` enqueues, on the current stream:
     the reduce-scatter-plus-gather kernel on every rank and, on the root, the wait for all slices.
     """
 
-    def __init__(self, n, n_classes, device, root=0, group=None, grid_blocks=32):
-        from torch.multiprocessing.reductions import reduce_tensor
+    def __init__(self, n, n_classes, device, root=0, group=None, grid_blocks=148, overlap=True):
         from . import _native
         self._lib = _native.load()
         self._check = _native.check
@@ -48,42 +47,93 @@ class PeerReducer:
             raise ValueError('n * n_classes must be a multiple of 4 for the peer reduce')
         self.grid_blocks = int(grid_blocks)
         self.step = 0
-        self.partial = [torch.zeros((n, n_classes), dtype=torch.float32, device=self.device) for _ in range(2)]
-        self.result = [torch.zeros((n, n_classes), dtype=torch.float32, device=self.device) for _ in range(2)]
-        self.flags = torch.zeros(2 * self.world + 1, dtype=torch.int32, device=self.device)
-        torch.cuda.synchronize(self.device)
-        mine = [reduce_tensor(t) for t in self.partial + self.result + [self.flags]]
+        # the reduce runs on its own stream so that it overlaps the next batch's fused kernel
+        self.overlap = bool(overlap)
+        self._side = torch.cuda.Stream(device=self.device) if self.overlap else None
+        self._ev_ready = [torch.cuda.Event() for _ in range(2)]
+        self._ev_done = [torch.cuda.Event() for _ in range(2)]
+        # one block per rank: partial[0] | partial[1] | result[0] | result[1] | flags
+        buf_bytes = (self.count * 4 + 255) // 256 * 256
+        self._offsets = [0, buf_bytes, 2 * buf_bytes, 3 * buf_bytes, 4 * buf_bytes]
+        total = 4 * buf_bytes + 256
+        base = ctypes.c_void_p()
+        handle = ctypes.create_string_buffer(64)
+        with torch.cuda.device(self.device):
+            self._check(self._lib.rfk_peer_alloc(total, ctypes.byref(base), handle))
+        self._base = base.value
         everyone = [None] * self.world
-        dist.all_gather_object(everyone, mine, group=group)
-        # keep the rebuilt tensors alive: they hold the IPC mappings
-        self._peer = []
-        for r, handles in enumerate(everyone):
-            if r == self.rank:
-                self._peer.append(self.partial + self.result + [self.flags])
-            else:
-                self._peer.append([fn(*args) for (fn, args) in handles])
+        dist.all_gather_object(everyone, (bytes(handle.raw), self.device.index), group=group)
+        self._bases, self._opened = [], []
+        with torch.cuda.device(self.device):      # map with MY device current: my kernels will touch it
+            for r, (h, peer_dev) in enumerate(everyone):
+                if r == self.rank:
+                    self._bases.append(self._base)
+                    continue
+                self._check(self._lib.rfk_peer_enable(int(peer_dev)))
+                p = ctypes.c_void_p()
+                self._check(self._lib.rfk_peer_open(ctypes.create_string_buffer(h, 64), ctypes.byref(p)))
+                self._bases.append(p.value)
+                self._opened.append(p.value)
         vp = ctypes.c_void_p
-        self._probs_ptrs = [(vp * self.world)(*[self._peer[r][k].data_ptr() for r in range(self.world)]) for k in (0, 1)]
-        self._flag_ptrs = (vp * self.world)(*[self._peer[r][4].data_ptr() for r in range(self.world)])
-        self._root_out = [self._peer[self.root][2 + k].data_ptr() for k in (0, 1)]
+        self._probs_ptrs = [(vp * self.world)(*[b + self._offsets[k] for b in self._bases]) for k in (0, 1)]
+        self._flag_ptrs = (vp * self.world)(*[b + self._offsets[4] for b in self._bases])
+        self._root_out = [self._bases[self.root] + self._offsets[2 + k] for k in (0, 1)]
+        self.partial = [self._as_tensor(self._base + self._offsets[k], (n, n_classes)) for k in (0, 1)]
+        self.result = [self._as_tensor(self._base + self._offsets[2 + k], (n, n_classes)) for k in (0, 1)]
+        self._flags_ptr = self._base + self._offsets[4]
         dist.barrier(group=group)
 
+    def _as_tensor(self, ptr, shape):
+        """A float32 torch view of raw device memory owned by this object."""
+        class _Holder:
+            pass
+        hld = _Holder()
+        hld.__cuda_array_interface__ = {'shape': tuple(shape), 'typestr': '<f4', 'data': (int(ptr), False), 'version': 2}
+        hld.owner = self
+        return torch.as_tensor(hld, device=self.device)
+
+    def close(self):
+        if getattr(self, '_base', None) is None:
+            return
+        torch.cuda.synchronize(self.device)
+        with torch.cuda.device(self.device):
+            for p in self._opened:
+                self._lib.rfk_peer_close(p)
+            self._lib.rfk_peer_free(self._base)
+        self._base = None
+
     def next_partial(self):
-        """The buffer this rank's fused kernel must write for the coming step."""
-        return self.partial[(self.step + 1) & 1]
+        """The buffer this rank's fused kernel must write for the coming step.  (Its previous
+        contents, two steps old, have been consumed: the current stream waits for that reduce.)"""
+        k = (self.step + 1) & 1
+        if self.overlap and self.step >= 2:
+            torch.cuda.current_stream(self.device).wait_event(self._ev_done[k])
+        return self.partial[k]
 
     def reduce(self):
         """Enqueue the cross-rank mean of the buffers handed out by ``next_partial``; returns the
         result tensor (meaningful on the root, once the stream has passed this point)."""
         self.step += 1
         k = self.step & 1
-        stream = ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+        cur = torch.cuda.current_stream(self.device)
+        run_on = self._side if self.overlap else cur
+        if self.overlap:
+            self._ev_ready[k].record(cur)               # the partials of this step are written
+            run_on.wait_event(self._ev_ready[k])
+        stream = ctypes.c_void_p(run_on.cuda_stream)
         with torch.cuda.device(self.device):
             self._check(self._lib.rfk_peer_reduce(self._probs_ptrs[k], self._flag_ptrs, self.world, self.rank, self.root,
                                                   self.step, self.count, self._root_out[k], self.grid_blocks, stream))
             if self.rank == self.root:
-                self._check(self._lib.rfk_peer_wait(self.flags.data_ptr(), self.world, self.step, stream))
+                self._check(self._lib.rfk_peer_wait(self._flags_ptr, self.world, self.step, stream))
+        if self.overlap:
+            self._ev_done[k].record(run_on)
         return self.result[k]
+
+    def wait(self, k=None):
+        """Make the current stream wait for the reduce of the last step (or of parity k)."""
+        if self.overlap:
+            torch.cuda.current_stream(self.device).wait_event(self._ev_done[self.step & 1 if k is None else k])
 
 
 class DistributedEnsemble:

@@ -323,3 +323,24 @@ def test_mixed_ensemble_with_an_external_plugin():
     want = ff.ensemble_predictions([gpu_probs.cpu().numpy().tolist(), tree.tolist()], 'IMAGE_CLASSIFICATION')
     assert np.array_equal(got, np.asarray(want).astype(np.float32))
     tr.close()
+
+
+def test_peer_reduce_single_rank_degenerates_to_a_rounded_copy():
+    """The cross-GPU kernel with a world of one (the multi-rank case needs several GPUs and is
+    checked by tools/check_peer_reduce.py under torchrun): flags, step counters and the slice
+    arithmetic must work, and two steps in a row must reuse the flag block without a reset."""
+    import ctypes
+    lib = _native.load()
+    n, c = 1000, 10
+    flags = torch.zeros(3, dtype=torch.int32, device='cuda')
+    for step in (1, 2):
+        part = torch.rand((n, c), dtype=torch.float32, device='cuda')
+        out = torch.zeros((n, c), dtype=torch.float32, device='cuda')
+        probs = (ctypes.c_void_p * 1)(part.data_ptr())
+        fl = (ctypes.c_void_p * 1)(flags.data_ptr())
+        _native.check(lib.rfk_peer_enable(0))
+        _native.check(lib.rfk_peer_reduce(probs, fl, 1, 0, 0, step, n * c, out.data_ptr(), 8, None))
+        _native.check(lib.rfk_peer_wait(flags.data_ptr(), 1, step, None))
+        torch.cuda.synchronize()
+        assert torch.equal(out, part)
+    assert flags.cpu().tolist() == [2, 2, 16]

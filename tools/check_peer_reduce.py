@@ -33,6 +33,7 @@ def main():
     for i in range(5):
         x = xs[i % 3]
         res = dens.forward_peer(x, red)
+        red.wait()
         dens.forward(x, out=out_nccl)
         torch.cuda.synchronize()
         if rank == 0:
@@ -51,6 +52,8 @@ def main():
         e0.record()
         for i in range(200):
             fn(xs[i % 3])
+        red.wait(0)
+        red.wait(1)
         e1.record()
         dist.barrier()
         torch.cuda.synchronize()
