@@ -203,7 +203,7 @@ def main():
     ap.add_argument('--workload', default='c3', choices=sorted(WORKLOADS))
     ap.add_argument('--compute', default='f16', choices=['f16', 'bf16', 'f32'])
     ap.add_argument('--no-cpu-baseline', action='store_true')
-    ap.add_argument('--reduce', default='peer', choices=['peer', 'nccl'],
+    ap.add_argument('--reduce', default='gather', choices=['gather', 'peer', 'nccl'],
                     help='N > 1, trial-per-GPU workloads: fused peer-memory reduce (default) or torch.distributed/NCCL')
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
@@ -248,9 +248,9 @@ def main():
     do_reduce = world > 1 and wl['scaling'] == 'strong' and wl.get('shard') != 'rows'
     dens = DistributedEnsemble(ens, W, C, dev, root=0) if do_reduce else None
     reducer = None
-    if do_reduce and args.reduce == 'peer':
-        from rafiki_b200.distributed import PeerReducer
-        reducer = PeerReducer(n, C, dev, root=0)
+    if do_reduce and args.reduce in ('peer', 'gather'):
+        from rafiki_b200.distributed import PeerGather, PeerReducer
+        reducer = (PeerGather if args.reduce == 'gather' else PeerReducer)(n, C, dev, root=0)
 
     outs = [out, torch.zeros_like(out)]
     pending = [None, None]
@@ -402,7 +402,8 @@ def main():
             'data': 'synthetic',
             'config': {'workload': wl['name'], 'trials': W, 'batch': n, 'd': d, 'hidden_units': wl['hidden'],
                        'hidden_layers': wl['layers'], 'classes': C,
-                       'parallelism': ('trial-per-gpu x{} + {}'.format(world, 'fused peer-memory reduce (NVLink)' if
+                       'parallelism': ('trial-per-gpu x{} + {}'.format(world, ('epilogue stores into the root over NVLink + sum' if args.reduce == 'gather' else
+                                                                        'peer-memory reduce-scatter kernel') if
                                                                        reducer is not None else 'nccl reduce')
                                        if do_reduce else
                                        ('rows sharded x{}'.format(world) if wl.get('shard') == 'rows' else

@@ -129,6 +129,8 @@ int rfk_mlp_forward_static(rfk_mlp_t* h, const uint8_t* x, int64_t n, float* pro
  * rounded once to float, so out equals float32(reference mean) bit for bit.
  */
 int rfk_ensemble_mean(const float* const* probs, int w, int64_t n, int c, float* out, void* stream);
+/* Same, without the division: out = float32(sum in float64) -- adds up the partial means of ranks. */
+int rfk_ensemble_sum(const float* const* probs, int w, int64_t n, int c, float* out, void* stream);
 
 /*
  * Kernels 1+2+3 for trials that live on one GPU: every trial's forward pass and the
@@ -170,6 +172,16 @@ int rfk_peer_reduce(const float* const* probs, unsigned int* const* flags, int w
                     int root, unsigned int step, int64_t count, float* root_out, int grid_blocks,
                     void* stream);
 int rfk_peer_wait(const unsigned int* flags_of_this_rank, int world, unsigned int step, void* stream);
+/*
+ * Gather form of the same collective, fused into the trial kernel: a rank passes rfk_ensemble_forward
+ * an `out` pointer that lies in the ROOT's memory (its slot of the root's rfk_peer_alloc block), so the
+ * kernel's epilogue stores the partial means across NVLink tile by tile while it computes.
+ * rfk_peer_signal, stream-ordered after that kernel, publishes "step s is in place" by storing `step`
+ * into `count` flags in peer memory (HOST array of DEVICE pointers); rfk_peer_wait_flags holds a stream until `count` consecutive flags have
+ * all reached `step`.  The root then adds its slots with rfk_ensemble_sum.
+ */
+int rfk_peer_signal(unsigned int* const* flags, int count, unsigned int step, void* stream);
+int rfk_peer_wait_flags(const unsigned int* flags, int count, unsigned int step, void* stream);
 
 #ifdef __cplusplus
 }

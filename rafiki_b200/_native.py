@@ -46,6 +46,7 @@ PROTOTYPES = {
     'rfk_mlp_forward': (_i, [_vp, _vp, _i64, _vp, _vp, _sz, _vp]),
     'rfk_mlp_forward_static': (_i, [_vp, _vp, _i64, _vp, _vp]),
     'rfk_ensemble_mean': (_i, [_c.POINTER(_vp), _i, _i64, _i, _vp, _vp]),
+    'rfk_ensemble_sum': (_i, [_c.POINTER(_vp), _i, _i64, _i, _vp, _vp]),
     'rfk_ensemble_workspace_bytes': (_i, [_c.POINTER(_vp), _i, _i64, _c.POINTER(_sz)]),
     'rfk_ensemble_forward': (_i, [_c.POINTER(_vp), _i, _i, _vp, _i64, _vp, _vp, _sz, _vp]),
     'rfk_peer_alloc': (_i, [_sz, _c.POINTER(_vp), _vp]),
@@ -55,6 +56,8 @@ PROTOTYPES = {
     'rfk_peer_enable': (_i, [_i]),
     'rfk_peer_reduce': (_i, [_c.POINTER(_vp), _c.POINTER(_vp), _i, _i, _i, _c.c_uint, _i64, _vp, _i, _vp]),
     'rfk_peer_wait': (_i, [_vp, _i, _c.c_uint, _vp]),
+    'rfk_peer_signal': (_i, [_c.POINTER(_vp), _i, _c.c_uint, _vp]),
+    'rfk_peer_wait_flags': (_i, [_vp, _i, _c.c_uint, _vp]),
 }
 
 _lib = None

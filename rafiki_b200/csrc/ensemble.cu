@@ -27,9 +27,10 @@ __device__ __forceinline__ float4 ld_stream_f4(const float* p) {
   return r;
 }
 
+// divisor = W for the mean; 1 for a plain float64 sum (partial means of several ranks)
 template <int W>
 __global__ void __launch_bounds__(kThreads)
-ensemble_mean_vec4_kernel(const TrialPtrs ptrs, int w_runtime, int64_t n_vec, float* __restrict__ out) {
+ensemble_mean_vec4_kernel(const TrialPtrs ptrs, int w_runtime, int64_t n_vec, float* __restrict__ out, double divisor) {
   const int w = W > 0 ? W : w_runtime;
   const int64_t stride = (int64_t)gridDim.x * kThreads;
   for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n_vec; i += stride) {
@@ -50,26 +51,40 @@ ensemble_mean_vec4_kernel(const TrialPtrs ptrs, int w_runtime, int64_t n_vec, fl
     }
     // np.mean divides the float64 sum by W (true division, not a multiply by 1/W)
     float4 o;
-    o.x = (float)(s0 / (double)w); o.y = (float)(s1 / (double)w);
-    o.z = (float)(s2 / (double)w); o.w = (float)(s3 / (double)w);
+    o.x = (float)(s0 / divisor); o.y = (float)(s1 / divisor);
+    o.z = (float)(s2 / divisor); o.w = (float)(s3 / divisor);
     *reinterpret_cast<float4*>(out + 4 * i) = o;
   }
 }
 
 __global__ void __launch_bounds__(kThreads)
-ensemble_mean_scalar_kernel(const TrialPtrs ptrs, int w, int64_t n_elems, float* __restrict__ out) {
+ensemble_mean_scalar_kernel(const TrialPtrs ptrs, int w, int64_t n_elems, float* __restrict__ out, double divisor) {
   const int64_t stride = (int64_t)gridDim.x * kThreads;
   for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n_elems; i += stride) {
     double s = 0.0;
     for (int t = 0; t < w; ++t) s += (double)ptrs.p[t][i];
-    out[i] = (float)(s / (double)w);
+    out[i] = (float)(s / divisor);
   }
 }
 
 }  // namespace
 
+namespace {
+int ensemble_reduce(const float* const* probs, int w, int64_t n, int c, float* out, void* stream, bool mean);
+}
+
 extern "C" int rfk_ensemble_mean(const float* const* probs, int w, int64_t n, int c, float* out,
                                  void* stream) {
+  return ensemble_reduce(probs, w, n, c, out, stream, true);
+}
+
+extern "C" int rfk_ensemble_sum(const float* const* probs, int w, int64_t n, int c, float* out, void* stream) {
+  return ensemble_reduce(probs, w, n, c, out, stream, false);
+}
+
+namespace {
+int ensemble_reduce(const float* const* probs, int w, int64_t n, int c, float* out, void* stream, bool mean) {
+  const double divisor = mean ? (double)w : 1.0;
   RFK_REQUIRE(w >= 1 && w <= RFK_MAX_TRIALS, "ensemble_mean: w=%d outside 1..%d", w, RFK_MAX_TRIALS);
   RFK_REQUIRE(n >= 0 && c >= 1, "ensemble_mean: bad shape n=%lld c=%d", (long long)n, c);
   if (n == 0) return RFK_OK;
@@ -90,22 +105,23 @@ extern "C" int rfk_ensemble_mean(const float* const* probs, int w, int64_t n, in
     const int64_t want = (n_vec + kThreads - 1) / kThreads;
     const int grid = (int)(want < (int64_t)sms * 8 ? want : (int64_t)sms * 8);
     switch (w) {
-      case 1: ensemble_mean_vec4_kernel<1><<<grid, kThreads, 0, st>>>(ptrs, w, n_vec, out); break;
-      case 2: ensemble_mean_vec4_kernel<2><<<grid, kThreads, 0, st>>>(ptrs, w, n_vec, out); break;
-      case 3: ensemble_mean_vec4_kernel<3><<<grid, kThreads, 0, st>>>(ptrs, w, n_vec, out); break;
-      case 4: ensemble_mean_vec4_kernel<4><<<grid, kThreads, 0, st>>>(ptrs, w, n_vec, out); break;
-      case 8: ensemble_mean_vec4_kernel<8><<<grid, kThreads, 0, st>>>(ptrs, w, n_vec, out); break;
-      default: ensemble_mean_vec4_kernel<0><<<grid, kThreads, 0, st>>>(ptrs, w, n_vec, out); break;
+      case 1: ensemble_mean_vec4_kernel<1><<<grid, kThreads, 0, st>>>(ptrs, w, n_vec, out, divisor); break;
+      case 2: ensemble_mean_vec4_kernel<2><<<grid, kThreads, 0, st>>>(ptrs, w, n_vec, out, divisor); break;
+      case 3: ensemble_mean_vec4_kernel<3><<<grid, kThreads, 0, st>>>(ptrs, w, n_vec, out, divisor); break;
+      case 4: ensemble_mean_vec4_kernel<4><<<grid, kThreads, 0, st>>>(ptrs, w, n_vec, out, divisor); break;
+      case 8: ensemble_mean_vec4_kernel<8><<<grid, kThreads, 0, st>>>(ptrs, w, n_vec, out, divisor); break;
+      default: ensemble_mean_vec4_kernel<0><<<grid, kThreads, 0, st>>>(ptrs, w, n_vec, out, divisor); break;
     }
     RFK_LAUNCH_CHECK("ensemble_mean_vec4_kernel");
   } else {
     const int64_t want = (elems + kThreads - 1) / kThreads;
     const int grid = (int)(want < (int64_t)sms * 8 ? want : (int64_t)sms * 8);
-    ensemble_mean_scalar_kernel<<<grid, kThreads, 0, st>>>(ptrs, w, elems, out);
+    ensemble_mean_scalar_kernel<<<grid, kThreads, 0, st>>>(ptrs, w, elems, out, divisor);
     RFK_LAUNCH_CHECK("ensemble_mean_scalar_kernel");
   }
   return RFK_OK;
 }
+}  // namespace
 
 namespace {
 __global__ void __launch_bounds__(kThreads)

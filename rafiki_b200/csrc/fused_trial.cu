@@ -73,11 +73,14 @@ constexpr int OFF_RAW = OFF_B + STAGES * B_STAGE;
 constexpr int OFF_W2 = OFF_RAW + RAW_STAGES * RAW_STAGE;
 constexpr int OFF_W3 = OFF_W2 + W2_BYTES;
 constexpr int OFF_BIAS = OFF_W3 + 2 * W3_BYTES;     // W3 is double buffered by item parity
-constexpr int OFF_BAR = OFF_BIAS + 2 * BIAS_BYTES;
+constexpr int OUT_BYTES = TILE_M * CPAD * 4;       // staging of one tile's probabilities for 16-byte stores
+constexpr int OFF_OUT = (OFF_BIAS + 2 * BIAS_BYTES + 15) / 16 * 16;
+constexpr int OFF_BAR = OFF_OUT + OUT_BYTES;
 constexpr int NUM_BARS = 2 * STAGES + 2 * RAW_STAGES + 17;
 constexpr int OFF_TMEM_SLOT = OFF_BAR + NUM_BARS * 8;
 constexpr int SMEM_USED = OFF_TMEM_SLOT + 16;
-constexpr int SMEM_BYTES = SMEM_USED + 1024;      // slack for the 1024-byte alignment of the base
+constexpr int SMEM_BYTES = SMEM_USED;             // the kernel has no static shared memory, so the dynamic
+                                                  // window starts 1024-byte aligned (checked at kernel entry)
 static_assert(OFF_W2 % 1024 == 0 && OFF_W3 % 1024 == 0 && OFF_B % 1024 == 0, "operand alignment");
 static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
 
@@ -246,12 +249,16 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
   }
   const long long t_start = kProf ? clock64() : 0;
   int trace_n = 0;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
   Bars* bars = reinterpret_cast<Bars*>(smem + OFF_BAR);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + OFF_TMEM_SLOT);
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  if ((smem_u32(smem) & 1023u) != 0u) {        // the swizzled operand tiles need 1024-byte alignment
+    if (threadIdx.x == 0) printf("rafiki_b200: dynamic shared memory is not 1024-byte aligned\n");
+    __trap();
+  }
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < STAGES; ++s) {
@@ -344,16 +351,33 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
         for (int j = 0; j < CPAD; ++j) acc[j] += (double)(z[j] * inv);
         if (warp == 0) RFK_TRACE(3, 6);
         if (prev_t == t1 - 1) {
-          // the tile's ensemble mean: float64 sum in trial order, one division, one rounding
-          const long long grow = (long long)prev_tile * TILE_M + row;
-          if (grow < P.n) {
-            float* o = P.out + (P.split ? (long long)t0 * P.n * P.n_classes : 0ll) + grow * P.n_classes;
+          // the tile's ensemble mean: float64 sum in trial order, one division, one rounding.  The
+          // 128 rows of a tile are one contiguous block of the output, so they are staged in shared
+          // memory and leave as 16-byte stores (the output may be peer memory across NVLink, where
+          // 4-byte stores would waste most of every packet).
+          const int C = P.n_classes;
+          float* stage = reinterpret_cast<float*>(smem + OFF_OUT);
 #pragma unroll
-            for (int j = 0; j < CPAD; ++j)
-              if (j < P.n_classes) o[j] = (float)(acc[j] / (double)(P.split ? 1 : P.total_trials));
-          }
+          for (int j = 0; j < CPAD; ++j)
+            if (j < C) stage[row * C + j] = (float)(acc[j] / (double)(P.split ? 1 : P.total_trials));
 #pragma unroll
           for (int j = 0; j < CPAD; ++j) acc[j] = 0.0;
+          asm volatile("bar.sync 1, 128;" ::: "memory");           // the four softmax warps
+          {
+            const long long first = (long long)prev_tile * TILE_M;
+            const long long rows = P.n - first < TILE_M ? P.n - first : TILE_M;
+            const int valid = (int)rows * C;                        // floats of this tile that exist
+            float* o = P.out + (P.split ? (long long)t0 * P.n * C : 0ll) + first * C;
+            if ((reinterpret_cast<uintptr_t>(o) & 15) == 0) {
+              const int nvec = valid >> 2;
+              for (int i = row; i < nvec; i += 128)
+                reinterpret_cast<float4*>(o)[i] = reinterpret_cast<const float4*>(stage)[i];
+              for (int i = (nvec << 2) + row; i < valid; i += 128) o[i] = stage[i];
+            } else {
+              for (int i = row; i < valid; i += 128) o[i] = stage[i];
+            }
+          }
+          asm volatile("bar.sync 1, 128;" ::: "memory");           // staging buffer free again
         }
       } else {
         mbar_arrive(&bars->bias_free[prev_buf]);

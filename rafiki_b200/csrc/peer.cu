@@ -24,7 +24,10 @@
 
 namespace {
 
-constexpr int kThreads = 256;
+// Small and register-light on purpose (128 threads, <= 32 registers): the fused kernel of the next
+// batch occupies every SM with 640 threads x 96 registers, which leaves 4096 registers per SM --
+// exactly one block of this kernel -- so the two really run side by side.
+constexpr int kThreads = 128;
 constexpr int kMaxRanks = 16;
 
 struct PeerPtrs {
@@ -56,7 +59,7 @@ __device__ __forceinline__ float4 ld_peer_f4(const float* p) {
   return r;
 }
 
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 16)
 peer_reduce_kernel(const PeerPtrs ptrs, int world, int rank, int root, unsigned int step, long long n_vec,
                    float* __restrict__ root_out) {
   unsigned int* mine = ptrs.flags[rank];
@@ -78,16 +81,14 @@ peer_reduce_kernel(const PeerPtrs ptrs, int world, int rank, int root, unsigned 
   const long long stride = (long long)gridDim.x * kThreads;
   for (long long i = lo + (long long)blockIdx.x * kThreads + threadIdx.x; i < hi; i += stride) {
     double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
-    // all ranks' loads are issued before the first sum: NVLink latency is paid once per element
-    float4 v[kMaxRanks];
-#pragma unroll
-    for (int j = 0; j < kMaxRanks; ++j)
-      if (j < world) v[j] = ld_peer_f4(ptrs.probs[j] + 4 * i);
-#pragma unroll
-    for (int j = 0; j < kMaxRanks; ++j)
-      if (j < world) {
-        s0 += (double)v[j].x; s1 += (double)v[j].y; s2 += (double)v[j].z; s3 += (double)v[j].w;
-      }
+    // rank j+1's load is in flight while rank j is added (two vectors live: the register budget)
+    float4 v = ld_peer_f4(ptrs.probs[0] + 4 * i);
+    for (int j = 1; j <= world; ++j) {
+      float4 nv = v;
+      if (j < world) nv = ld_peer_f4(ptrs.probs[j] + 4 * i);
+      s0 += (double)v.x; s1 += (double)v.y; s2 += (double)v.z; s3 += (double)v.w;
+      v = nv;
+    }
     float4 o;
     o.x = (float)s0; o.y = (float)s1; o.z = (float)s2; o.w = (float)s3;
     *reinterpret_cast<float4*>(root_out + 4 * i) = o;
@@ -103,6 +104,15 @@ peer_reduce_kernel(const PeerPtrs ptrs, int world, int rank, int root, unsigned 
       st_release_sys(ptrs.flags[root] + world + rank, step);
     }
   }
+}
+
+struct FlagPtrs {
+  unsigned int* p[kMaxRanks];
+};
+__global__ void peer_signal_kernel(const FlagPtrs flags, int count, unsigned int step) {
+  // everything this stream did before (the fused kernel's stores into peer memory) is ordered first
+  __threadfence_system();
+  if (threadIdx.x < count) st_release_sys(flags.p[threadIdx.x], step);
 }
 
 __global__ void peer_wait_kernel(const unsigned int* done_flags, int world, unsigned int step) {
@@ -192,6 +202,23 @@ extern "C" int rfk_peer_reduce(const float* const* probs, unsigned int* const* f
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   peer_reduce_kernel<<<grid_blocks, kThreads, 0, st>>>(p, world, rank, root, step, count / 4, root_out);
   RFK_LAUNCH_CHECK("peer_reduce_kernel");
+  return RFK_OK;
+}
+
+extern "C" int rfk_peer_signal(unsigned int* const* flags, int count, unsigned int step, void* stream) {
+  RFK_REQUIRE(flags != nullptr && count >= 1 && count <= kMaxRanks, "peer_signal: bad argument");
+  FlagPtrs f;
+  for (int i = 0; i < kMaxRanks; ++i) f.p[i] = i < count ? flags[i] : nullptr;
+  for (int i = 0; i < count; ++i) RFK_REQUIRE(flags[i] != nullptr, "peer_signal: flag %d is NULL", i);
+  peer_signal_kernel<<<1, 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(f, count, step);
+  RFK_LAUNCH_CHECK("peer_signal_kernel");
+  return RFK_OK;
+}
+
+extern "C" int rfk_peer_wait_flags(const unsigned int* flags, int count, unsigned int step, void* stream) {
+  RFK_REQUIRE(flags != nullptr && count >= 1 && count <= kMaxRanks, "peer_wait_flags: bad argument");
+  peer_wait_kernel<<<1, 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(flags, count, step);
+  RFK_LAUNCH_CHECK("peer_wait_kernel");
   return RFK_OK;
 }
 

@@ -34,7 +34,7 @@ class PeerReducer:
     the reduce-scatter-plus-gather kernel on every rank and, on the root, the wait for all slices.
     """
 
-    def __init__(self, n, n_classes, device, root=0, group=None, grid_blocks=148, overlap=True):
+    def __init__(self, n, n_classes, device, root=0, group=None, grid_blocks=296, overlap=True):
         from . import _native
         self._lib = _native.load()
         self._check = _native.check
@@ -134,6 +134,88 @@ class PeerReducer:
         """Make the current stream wait for the reduce of the last step (or of parity k)."""
         if self.overlap:
             torch.cuda.current_stream(self.device).wait_event(self._ev_done[self.step & 1 if k is None else k])
+
+
+class PeerGather(PeerReducer):
+    """The same collective fused into the trial kernel itself: a rank's fused kernel is handed an
+    output pointer that lies in the ROOT's memory (its slot of the root's block), so the epilogue
+    stores its partial means across NVLink tile by tile while the tensor cores work on the next tile.
+    After the kernel each rank raises a flag on the root; the root waits for all flags, adds the G
+    slots (``rfk_ensemble_sum``, float64) and acknowledges, which frees the slots for the step after
+    next.  No separate communication kernel runs on the non-root ranks at all.
+    """
+
+    def __init__(self, n, n_classes, device, root=0, group=None):
+        from . import _native
+        self._lib = _native.load()
+        self._check = _native.check
+        self.device = torch.device(device)
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        self.root = root
+        self.n, self.n_classes = int(n), int(n_classes)
+        self.count = self.n * self.n_classes
+        self.step = 0
+        self.overlap = False
+        G = self.world
+        buf_bytes = (self.count * 4 + 255) // 256 * 256
+        self._buf_bytes = buf_bytes
+        self._flags_off = (2 * G + 2) * buf_bytes           # [0,G): arrived (on the root); [G]: consumed (on each rank)
+        total = self._flags_off + 256
+        base = ctypes.c_void_p()
+        handle = ctypes.create_string_buffer(64)
+        with torch.cuda.device(self.device):
+            self._check(self._lib.rfk_peer_alloc(total, ctypes.byref(base), handle))
+        self._base = base.value
+        everyone = [None] * G
+        dist.all_gather_object(everyone, (bytes(handle.raw), self.device.index), group=group)
+        self._bases, self._opened = [], []
+        with torch.cuda.device(self.device):
+            for r, (h, peer_dev) in enumerate(everyone):
+                if r == self.rank:
+                    self._bases.append(self._base)
+                    continue
+                self._check(self._lib.rfk_peer_enable(int(peer_dev)))
+                p = ctypes.c_void_p()
+                self._check(self._lib.rfk_peer_open(ctypes.create_string_buffer(h, 64), ctypes.byref(p)))
+                self._bases.append(p.value)
+                self._opened.append(p.value)
+        root_base = self._bases[self.root]
+        vp = ctypes.c_void_p
+        # my slot in the root's block, per parity, as a tensor my fused kernel can be pointed at
+        self.partial = [self._as_tensor(root_base + (k * G + self.rank) * buf_bytes, (n, n_classes)) for k in (0, 1)]
+        self.result = [self._as_tensor(self._base + (2 * G + k) * buf_bytes, (n, n_classes)) for k in (0, 1)]
+        self._my_arrived = (vp * 1)(root_base + self._flags_off + 4 * self.rank)
+        self._consumed_local = self._base + self._flags_off + 4 * G
+        if self.rank == self.root:
+            self._slot_ptrs = [(vp * G)(*[self._base + (k * G + r) * buf_bytes for r in range(G)]) for k in (0, 1)]
+            self._ack_ptrs = (vp * G)(*[b + self._flags_off + 4 * G for b in self._bases])
+        dist.barrier(group=group)
+
+    def next_partial(self):
+        k = (self.step + 1) & 1
+        if self.step >= 2:      # the root must have added the slot's previous contents (two steps ago)
+            stream = ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+            with torch.cuda.device(self.device):
+                self._check(self._lib.rfk_peer_wait_flags(self._consumed_local, 1, self.step - 1, stream))
+        return self.partial[k]
+
+    def reduce(self):
+        self.step += 1
+        k = self.step & 1
+        stream = ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+        G = self.world
+        with torch.cuda.device(self.device):
+            self._check(self._lib.rfk_peer_signal(self._my_arrived, 1, self.step, stream))
+            if self.rank == self.root:
+                self._check(self._lib.rfk_peer_wait_flags(self._base + self._flags_off, G, self.step, stream))
+                self._check(self._lib.rfk_ensemble_sum(self._slot_ptrs[k], G, self.n, self.n_classes,
+                                                      self.result[k].data_ptr(), stream))
+                self._check(self._lib.rfk_peer_signal(self._ack_ptrs, G, self.step, stream))
+        return self.result[k]
+
+    def wait(self, k=None):
+        pass
 
 
 class DistributedEnsemble:

@@ -11,7 +11,7 @@ import torch.distributed as dist
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from oracle import feedforward as ff                                 # noqa: E402
 from rafiki_b200 import engine, synth                                # noqa: E402
-from rafiki_b200.distributed import DistributedEnsemble, PeerReducer, trials_of_rank   # noqa: E402
+from rafiki_b200.distributed import DistributedEnsemble, PeerGather, PeerReducer, trials_of_rank   # noqa: E402
 
 
 def main():
@@ -26,7 +26,7 @@ def main():
     trials = [engine.Trial(params[t]) for t in mine]
     ens = engine.Ensemble(trials, total_trials=W) if trials else None
     dens = DistributedEnsemble(ens, W, 10, dev)
-    red = PeerReducer(n, 10, dev)
+    red = PeerGather(n, 10, dev) if os.environ.get('RFK_PEER_MODE', 'gather') == 'gather' else PeerReducer(n, 10, dev)
     xs = [torch.from_numpy(synth.make_queries(n, 28, 1, 'uniform', seed=i, dead=dead)).to(dev) for i in range(3)]
     out_nccl = torch.zeros((n, 10), dtype=torch.float32, device=dev)
     ok = True
