@@ -203,7 +203,7 @@ def main():
     ap.add_argument('--workload', default='c3', choices=sorted(WORKLOADS))
     ap.add_argument('--compute', default='f16', choices=['f16', 'bf16', 'f32'])
     ap.add_argument('--no-cpu-baseline', action='store_true')
-    ap.add_argument('--reduce', default='gather', choices=['gather', 'peer', 'nccl'],
+    ap.add_argument('--reduce', default='peer', choices=['peer', 'gather', 'nccl'],
                     help='N > 1, trial-per-GPU workloads: fused peer-memory reduce (default) or torch.distributed/NCCL')
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]

@@ -34,7 +34,7 @@ class PeerReducer:
     the reduce-scatter-plus-gather kernel on every rank and, on the root, the wait for all slices.
     """
 
-    def __init__(self, n, n_classes, device, root=0, group=None, grid_blocks=296, overlap=True):
+    def __init__(self, n, n_classes, device, root=0, group=None, grid_blocks=148, overlap=False):
         from . import _native
         self._lib = _native.load()
         self._check = _native.check
@@ -121,11 +121,12 @@ class PeerReducer:
             self._ev_ready[k].record(cur)               # the partials of this step are written
             run_on.wait_event(self._ev_ready[k])
         stream = ctypes.c_void_p(run_on.cuda_stream)
-        with torch.cuda.device(self.device):
-            self._check(self._lib.rfk_peer_reduce(self._probs_ptrs[k], self._flag_ptrs, self.world, self.rank, self.root,
-                                                  self.step, self.count, self._root_out[k], self.grid_blocks, stream))
-            if self.rank == self.root:
-                self._check(self._lib.rfk_peer_wait(self._flags_ptr, self.world, self.step, stream))
+        if torch.cuda.current_device() != self.device.index:
+            torch.cuda.set_device(self.device)       # one process per GPU: this rank only ever uses its own device
+        self._check(self._lib.rfk_peer_reduce(self._probs_ptrs[k], self._flag_ptrs, self.world, self.rank, self.root,
+                                              self.step, self.count, self._root_out[k], self.grid_blocks, stream))
+        if self.rank == self.root:
+            self._check(self._lib.rfk_peer_wait(self._flags_ptr, self.world, self.step, stream))
         if self.overlap:
             self._ev_done[k].record(run_on)
         return self.result[k]

@@ -123,6 +123,7 @@ class Ensemble:
         self.total_trials = len(trials) if total_trials is None else int(total_trials)
         self._handles = _native.handle_array([t.handle for t in self.trials])
         self._ws = _Workspace(self.device)
+        self._ws_bytes = {}
         self.fused = all(t.fused for t in self.trials)
 
     def workspace_bytes(self, n):
@@ -134,11 +135,19 @@ class Ensemble:
         n = _check_queries(x, self.d)
         if out is None:
             out = torch.empty((n, self.n_classes), dtype=torch.float32, device=self.device)
-        ws, ws_bytes = self._ws.get(self.workspace_bytes(n))
-        with torch.cuda.device(self.device):
+        need = self._ws_bytes.get(n)
+        if need is None:
+            need = self._ws_bytes[n] = self.workspace_bytes(n)
+        ws, ws_bytes = self._ws.get(need)
+        if torch.cuda.current_device() == self.device.index:      # the common case: no device switch
             _native.check(self._lib.rfk_ensemble_forward(self._handles, len(self.trials), self.total_trials,
                                                          x.data_ptr(), n, out.data_ptr(), ws, ws_bytes,
                                                          _stream_ptr(stream)))
+        else:
+            with torch.cuda.device(self.device):
+                _native.check(self._lib.rfk_ensemble_forward(self._handles, len(self.trials), self.total_trials,
+                                                             x.data_ptr(), n, out.data_ptr(), ws, ws_bytes,
+                                                             _stream_ptr(stream)))
         return out
 
 
