@@ -54,12 +54,12 @@ constexpr int TILE_M = 128;
 constexpr int ATOM_K = 64;      // K elements of one 128-byte swizzle atom of 16-bit operands
 constexpr int KB = 128;         // K elements per pipeline step: two atoms, so that every barrier round
                                 // (loader -> converter -> MMA issuer) carries eight MMAs instead of four
-constexpr int STAGES = 2;       // A / B operand ring
+constexpr int A_STAGES = 2;     // A operand ring: converted query tile, in TENSOR memory (64 columns per stage)
+constexpr int B_STAGES = 4;     // B operand ring: first-layer weight blocks in shared memory; deep, because a
+                                // 32 KB block takes 1000-1500 cycles to arrive from L2 under load
 constexpr int RAW_STAGES = 3;   // raw uint8 ring (TMA landing zone; covers HBM latency)
 constexpr int HMAX = 128;       // widest hidden layer the fused path takes
 constexpr int CPAD = 16;        // class dimension padded to one UMMA N step
-constexpr int A_ATOM = TILE_M * 128;              // one 64-wide atom of the A tile
-constexpr int A_STAGE = (KB / ATOM_K) * A_ATOM;
 constexpr int B_STAGE = (KB / ATOM_K) * HMAX * 128;
 constexpr int RAW_STAGE = TILE_M * KB;            // 8192 bytes of uint8
 constexpr int W2_BYTES = 2 * HMAX * 128;
@@ -67,21 +67,20 @@ constexpr int W3_BYTES = 2 * CPAD * 128;
 constexpr int BIAS_FLOATS = HMAX + HMAX + CPAD;   // b1 | b2 | b3
 constexpr int BIAS_BYTES = BIAS_FLOATS * 4;
 
-constexpr int OFF_A = 0;
-constexpr int OFF_B = OFF_A + STAGES * A_STAGE;
-constexpr int OFF_RAW = OFF_B + STAGES * B_STAGE;
+constexpr int OFF_B = 0;
+constexpr int OFF_RAW = OFF_B + B_STAGES * B_STAGE;
 constexpr int OFF_W2 = OFF_RAW + RAW_STAGES * RAW_STAGE;
 constexpr int OFF_W3 = OFF_W2 + W2_BYTES;
 constexpr int OFF_BIAS = OFF_W3 + 2 * W3_BYTES;     // W3 is double buffered by item parity
 constexpr int OUT_BYTES = TILE_M * CPAD * 4;       // staging of one tile's probabilities for 16-byte stores
 constexpr int OFF_OUT = (OFF_BIAS + 2 * BIAS_BYTES + 15) / 16 * 16;
 constexpr int OFF_BAR = OFF_OUT + OUT_BYTES;
-constexpr int NUM_BARS = 2 * STAGES + 2 * RAW_STAGES + 17;
+constexpr int NUM_BARS = A_STAGES + 2 * B_STAGES + 2 * RAW_STAGES + 17;
 constexpr int OFF_TMEM_SLOT = OFF_BAR + NUM_BARS * 8;
 constexpr int SMEM_USED = OFF_TMEM_SLOT + 16;
 constexpr int SMEM_BYTES = SMEM_USED;             // the kernel has no static shared memory, so the dynamic
                                                   // window starts 1024-byte aligned (checked at kernel entry)
-static_assert(OFF_W2 % 1024 == 0 && OFF_W3 % 1024 == 0 && OFF_B % 1024 == 0, "operand alignment");
+static_assert(OFF_W2 % 1024 == 0 && OFF_W3 % 1024 == 0 && OFF_B % 1024 == 0 && OFF_RAW % 1024 == 0, "operand alignment");
 static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
 
 // Five warpgroups (setmaxnreg works per warpgroup): 0-1 epilogue, 2-3 converters, 4 = loader, MMA
@@ -89,18 +88,19 @@ static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
 // the light roles give registers back and the epilogue warps take them.
 constexpr int kEpiWarps = 8, kConvWarps = 8;
 constexpr int kEpiThreads = kEpiWarps * 32;                   // 256
-constexpr int kConvThreads = kConvWarps * 32;                 // 256: four 16-byte pieces per thread per step
-constexpr int kConvPieces = (TILE_M * KB / 16) / kConvThreads;   // 4
+constexpr int kConvThreads = kConvWarps * 32;                 // 256: half a row (64 bytes) per thread per step
 constexpr int kThreads = (kEpiWarps + kConvWarps + 4) * 32;   // 640
 constexpr int WARP_LOAD = kEpiWarps + kConvWarps, WARP_MMA = WARP_LOAD + 1, WARP_PAR = WARP_LOAD + 2,
               WARP_TAIL = WARP_LOAD + 3;
 constexpr int kRegsEpi = 136, kRegsLight = 56;
 
 constexpr int TMEM_COLS = 512;
-constexpr int COL_ACC1 = 0;     // two buffers of 128 columns
-constexpr int COL_ACC2 = 256;
-constexpr int COL_ACC3 = 384;
-constexpr int COL_HID = 400;     // hidden activations, 16-bit pairs: 64 columns (the next layer's A operand)
+constexpr int COL_ACC1 = 0;     // two buffers of 128 columns; layer 2 accumulates into the buffer its own
+                                // layer-1 epilogue has just drained
+constexpr int COL_A = 256;      // A operand ring of layer 1: A_STAGES x 64 columns of 16-bit pairs
+constexpr int COL_HID = 384;    // hidden activations, 16-bit pairs: 64 columns (the next layer's A operand)
+constexpr int COL_ACC3 = 448;
+static_assert(COL_A + A_STAGES * (KB / 2) <= COL_HID && COL_ACC3 + CPAD <= TMEM_COLS, "tensor memory map");
 
 struct TrialDev {
   const uint8_t* w1;    // [n_kb][h1_pad] rows of 128 B, swizzled
@@ -116,13 +116,15 @@ struct FusedParams {
   long long n;
   int d, n_kb, w, total_trials, n_classes, n_tiles;
   long long* prof;   // development only (RFK_FUSED_PROF): PF_COUNT counters, summed over CTAs
-  long long* trace;  // development only (RFK_FUSED_PROF=2): block 0 event timestamps, [4 roles][kTraceLen]
+  long long* trace;  // development only (RFK_FUSED_PROF=2): block 0 event timestamps, [5 roles][kTraceLen]
   int split;         // 1: one (tile, trial) item per CTA, per-trial probabilities to out[t][n][C] (small batches)
   int debug;         // development only (RFK_FUSED_DEBUG): 1 skip W1 copies, 2 skip conversion, 4 skip layer-1 MMAs
 };
 
 struct Bars {
-  uint64_t full[STAGES], empty[STAGES];           // A/B operand ring
+  uint64_t a_full[A_STAGES];                      // converters -> MMA issuer
+  uint64_t b_full[B_STAGES];                      // weight block landed
+  uint64_t step_done[B_STAGES];                   // MMAs of a step complete: frees its B stage and its A stage
   uint64_t raw_full[RAW_STAGES], raw_empty[RAW_STAGES];
   uint64_t acc1_full[2], acc1_empty[2];
   uint64_t hid_ready, acc2_full, acc3_full;
@@ -212,6 +214,21 @@ __device__ __forceinline__ void epilogue_hidden(uint32_t tmem_row_addr, int c_be
   tmem_st_wait();
 }
 
+// One arrival per warp instead of one per thread: 32 arrivals on one mbarrier serialise in the
+// shared-memory atomic unit (~1 lane per cycle).  __syncwarp orders the lanes' earlier writes
+// (and their proxy / tcgen05 fences) before the elected lane's release-arrive.
+__device__ __forceinline__ void warp_arrive(uint64_t* bar) {
+  __syncwarp();
+  if ((threadIdx.x & 31) == 0) mbar_arrive(bar);
+}
+__device__ __forceinline__ void warp_arrive2(uint64_t* bar_a, uint64_t* bar_b) {
+  __syncwarp();
+  if ((threadIdx.x & 31) == 0) {
+    mbar_arrive(bar_a);
+    mbar_arrive(bar_b);
+  }
+}
+
 // kProf (development, RFK_FUSED_PROF=1): the leader thread of each warp role accumulates the
 // cycles it spends blocked on each kind of barrier and adds them to P.prof at exit.
 enum ProfSlot { PF_EPI_BIAS, PF_EPI_ACC1, PF_EPI_ACC2, PF_EPI_ACC3, PF_EPI_TOTAL, PF_CONV_RAW, PF_CONV_EMPTY,
@@ -261,21 +278,22 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
   }
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < STAGES; ++s) {
-      mbar_init(&bars->full[s], kConvThreads + 1);
-      mbar_init(&bars->empty[s], 1);
+    for (int s = 0; s < A_STAGES; ++s) mbar_init(&bars->a_full[s], kConvWarps);
+    for (int s = 0; s < B_STAGES; ++s) {
+      mbar_init(&bars->b_full[s], 1);
+      mbar_init(&bars->step_done[s], 1);
     }
     for (int s = 0; s < RAW_STAGES; ++s) {
       mbar_init(&bars->raw_full[s], 1);
-      mbar_init(&bars->raw_empty[s], kConvThreads);
+      mbar_init(&bars->raw_empty[s], kConvWarps);
     }
     for (int b = 0; b < 2; ++b) {
       mbar_init(&bars->acc1_full[b], 1);
-      mbar_init(&bars->acc1_empty[b], kEpiThreads);
+      mbar_init(&bars->acc1_empty[b], kEpiWarps);
       mbar_init(&bars->bias_full[b], 1);
-      mbar_init(&bars->bias_free[b], kEpiThreads);
+      mbar_init(&bars->bias_free[b], kEpiWarps);
     }
-    mbar_init(&bars->hid_ready, kEpiThreads);
+    mbar_init(&bars->hid_ready, kEpiWarps);
     mbar_init(&bars->acc2_full, 1);
     mbar_init(&bars->acc3_full, 1);
     mbar_init(&bars->w2_full, 1);
@@ -346,7 +364,7 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
           sum += z[j];
         }
         const float inv = 1.0f / sum;
-        mbar_arrive(&bars->bias_free[prev_buf]);
+        warp_arrive(&bars->bias_free[prev_buf]);
 #pragma unroll
         for (int j = 0; j < CPAD; ++j) acc[j] += (double)(z[j] * inv);
         if (warp == 0) RFK_TRACE(3, 6);
@@ -380,7 +398,7 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
           asm volatile("bar.sync 1, 128;" ::: "memory");           // staging buffer free again
         }
       } else {
-        mbar_arrive(&bars->bias_free[prev_buf]);
+        warp_arrive(&bars->bias_free[prev_buf]);
       }
     };
     auto fetch_prev_logits = [&](uint32_t parity) {
@@ -395,7 +413,14 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
     };
     int item = 0;
     uint32_t acc2_phase = 0;          // acc2_full completes one phase per two-hidden-layer item only
-    for (int tile = tile0; tile < P.n_tiles; tile += tile_step) {
+    if (P.debug & 64) {               // development: layer-1 pipeline alone (no epilogue work, no layers 2/3)
+      for (int tile = tile0; tile < P.n_tiles; tile += tile_step)
+        for (int t = t0; t < t1; ++t, ++item) {
+          mbar_wait(&bars->acc1_full[item & 1], (uint32_t)((item >> 1) & 1));
+          warp_arrive(&bars->acc1_empty[item & 1]);
+        }
+    }
+    for (int tile = tile0; tile < ((P.debug & 64) ? 0 : P.n_tiles); tile += tile_step) {
       for (int t = t0; t < t1; ++t, ++item) {
         const TrialDev& T = P.trial[t];
         const int buf = item & 1;
@@ -413,8 +438,11 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
                                 hid_row_addr);
         }
         tc_fence_before_sync();
-        mbar_arrive(&bars->acc1_empty[buf]);
-        mbar_arrive(&bars->hid_ready);
+        // two-hidden-layer items keep the accumulator: layer 2 accumulates into it (see below)
+        if (T.n_hidden == 2)
+          warp_arrive(&bars->hid_ready);
+        else
+          warp_arrive2(&bars->acc1_empty[buf], &bars->hid_ready);
         if (warp == 0) RFK_TRACE(3, 2);
         // ---- deferred softmax of the previous item, overlapping this item's layer-2 MMAs
         if (have_prev) finish_prev();
@@ -425,10 +453,11 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
           acc2_phase ^= 1u;
           tc_fence_after_sync();
           const int split = T.h2_pad < 64 ? T.h2_pad : 64;
-          epilogue_hidden<kF16>(lane_addr + COL_ACC2, half ? split : 0, half ? T.h2_pad : split, bias + HMAX,
+          // layer 2 accumulated into this item's (drained) layer-1 buffer
+          epilogue_hidden<kF16>(lane_addr + COL_ACC1 + buf * HMAX, half ? split : 0, half ? T.h2_pad : split, bias + HMAX,
                                 hid_row_addr);
           tc_fence_before_sync();
-          mbar_arrive(&bars->hid_ready);
+          warp_arrive2(&bars->acc1_empty[buf], &bars->hid_ready);
           if (warp == 0) RFK_TRACE(3, 4);
         }
         have_prev = true;
@@ -444,59 +473,60 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
     }
   } else if (warp < kEpiWarps + kConvWarps) {
     // =============================================================== converter warps
-    // One step = one 64-wide K block of one item: 128 rows x 64 bytes of uint8 in the raw ring.
-    // Thread tp owns the 16-byte pieces (row = it*64 + tp/4, quarter = tp%4), it = 0..1; all
-    // offsets are fixed per thread, so a step is 2 x (LDS.128, 16 conversions, 2 x STS.128).
+    // One step = 128 K elements of one item: 128 rows x 128 bytes of uint8 in the raw ring (written by
+    // TMA with the 128-byte swizzle: 16-byte chunk c of row r sits at chunk position c ^ (r & 7), so
+    // the eight lanes of a quarter-warp, which read the same chunk of eight consecutive rows, hit
+    // eight different bank groups).  A thread owns half a row (warp % 4 = the TMEM lane quarter of
+    // the row, warp / 4 = which 64 bytes): 4 x LDS.128, 32 exact conversions, and the 64 operand
+    // values go straight into TENSOR memory (tcgen05.st), where the layer-1 MMAs read their A
+    // operand -- the converted tile never touches shared memory.
     asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsLight));
-    const int tp = threadIdx.x - kEpiThreads;                    // 0..255
-    const int q = tp & 7;                                        // 16-byte piece of the 128-byte raw row
-    const int r0 = tp >> 3;                                      // 0..31
-    const uint32_t sw = (uint32_t)(r0 & 7);
-    const uint32_t raw_off = smem_base + OFF_RAW + (uint32_t)r0 * KB + (uint32_t)q * 16u;
-    // piece q covers K elements 16q..16q+15 of the step: atom q / 4, 16-byte chunks 2(q%4), 2(q%4)+1
-    const uint32_t a_row = smem_base + OFF_A + (uint32_t)(q >> 2) * A_ATOM + (uint32_t)r0 * 128u;
-    const uint32_t a_off_lo = a_row + ((((uint32_t)(2 * (q & 3))) ^ sw) << 4);
-    const uint32_t a_off_hi = a_row + ((((uint32_t)(2 * (q & 3) + 1)) ^ sw) << 4);
-    constexpr uint32_t kRowsPerPass = TILE_M / kConvPieces;      // 32
-    int stage = 0, rstage = 0;
-    uint32_t phase = 0, rphase = 0;
-    // the probes of step s+1's barriers are issued while step s is converted
-    bool raw_ready = false, slot_ready = false;
+    const int quarter = warp & 3;
+    const int khalf = (warp - kEpiWarps) >> 2;
+    const int row = quarter * 32 + lane;
+    const uint32_t raw_row = smem_base + OFF_RAW + (uint32_t)row * 128u;
+    const uint32_t sw = (uint32_t)(row & 7);
+    uint32_t raw_chunk[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) raw_chunk[j] = raw_row + ((((uint32_t)(4 * khalf + j)) ^ sw) << 4);
+    const uint32_t a_dst0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + COL_A + (uint32_t)khalf * 32u;
+    int rstage = 0;
+    uint32_t rphase = 0;
+    int gs = 0;                                    // global step counter of this CTA
     for (int tile = tile0; tile < P.n_tiles; tile += tile_step) {
       for (int t = t0; t < t1; ++t) {
-        for (int kb = 0; kb < n_kb; ++kb) {
-          if (!raw_ready) mbar_wait(&bars->raw_full[rstage], rphase);
-          if (!slot_ready) mbar_wait(&bars->empty[stage], phase ^ 1u);
-          // columns past the end of the row are never read by the MMAs: skip their conversion
-          const bool live = !(P.debug & 2) && (kb * KB + q * 16 < P.d);
-          if (!live) raw_ready = slot_ready = false;
-          if (live) {
-            const uint32_t rsrc = raw_off + (uint32_t)rstage * RAW_STAGE;
-            const uint32_t dlo = a_off_lo + (uint32_t)stage * A_STAGE;
-            const uint32_t dhi = a_off_hi + (uint32_t)stage * A_STAGE;
-            uint4 raw[kConvPieces];
+        for (int kb = 0; kb < n_kb; ++kb, ++gs) {
+          mbar_wait(&bars->raw_full[rstage], rphase);
+          // A stage gs % 2 was last read by the MMAs of step gs - 2
+          if (gs >= A_STAGES) mbar_wait(&bars->step_done[(gs - A_STAGES) % B_STAGES], (uint32_t)(((gs - A_STAGES) / B_STAGES) & 1));
+          if (warp == kEpiWarps) RFK_TRACE(0, 1);
+          tc_fence_after_sync();
+          // 16-byte chunks of this thread's half row that the MMAs will read (the row may end inside the step)
+          int live = (P.d - kb * KB - khalf * 64 + 15) >> 4;
+          live = (P.debug & 2) ? 0 : (live < 0 ? 0 : (live > 4 ? 4 : live));
+          const uint32_t rsrc = (uint32_t)rstage * RAW_STAGE;
+          const uint32_t dst = a_dst0 + (uint32_t)(gs % A_STAGES) * (KB / 2);
 #pragma unroll
-            for (int it = 0; it < kConvPieces; ++it) raw[it] = lds_u4(rsrc + (uint32_t)it * (kRowsPerPass * KB));
-            {   // look ahead while the loads are in flight
-              const int ns = stage + 1 == STAGES ? 0 : stage + 1, nr = rstage + 1 == RAW_STAGES ? 0 : rstage + 1;
-              raw_ready = mbar_test(&bars->raw_full[nr], nr == 0 ? rphase ^ 1u : rphase);
-              slot_ready = mbar_test(&bars->empty[ns], (ns == 0 ? phase ^ 1u : phase) ^ 1u);
-            }
-#pragma unroll
-            for (int it = 0; it < kConvPieces; ++it) {
-              const uint4 lo = make_uint4(u8x2_to_op<kF16>(raw[it].x, 0), u8x2_to_op<kF16>(raw[it].x, 2),
-                                          u8x2_to_op<kF16>(raw[it].y, 0), u8x2_to_op<kF16>(raw[it].y, 2));
-              const uint4 hi = make_uint4(u8x2_to_op<kF16>(raw[it].z, 0), u8x2_to_op<kF16>(raw[it].z, 2),
-                                          u8x2_to_op<kF16>(raw[it].w, 0), u8x2_to_op<kF16>(raw[it].w, 2));
-              sts_u4(dlo + (uint32_t)it * (kRowsPerPass * 128u), lo);
-              sts_u4(dhi + (uint32_t)it * (kRowsPerPass * 128u), hi);
+          for (int h2 = 0; h2 < 2; ++h2) {
+            if (live > 2 * h2) {                   // warp-uniform
+              const uint4 r0 = lds_u4(raw_chunk[2 * h2] + rsrc), r1 = lds_u4(raw_chunk[2 * h2 + 1] + rsrc);
+              uint32_t p[16];
+              p[0] = u8x2_to_op<kF16>(r0.x, 0);  p[1] = u8x2_to_op<kF16>(r0.x, 2);
+              p[2] = u8x2_to_op<kF16>(r0.y, 0);  p[3] = u8x2_to_op<kF16>(r0.y, 2);
+              p[4] = u8x2_to_op<kF16>(r0.z, 0);  p[5] = u8x2_to_op<kF16>(r0.z, 2);
+              p[6] = u8x2_to_op<kF16>(r0.w, 0);  p[7] = u8x2_to_op<kF16>(r0.w, 2);
+              p[8] = u8x2_to_op<kF16>(r1.x, 0);  p[9] = u8x2_to_op<kF16>(r1.x, 2);
+              p[10] = u8x2_to_op<kF16>(r1.y, 0); p[11] = u8x2_to_op<kF16>(r1.y, 2);
+              p[12] = u8x2_to_op<kF16>(r1.z, 0); p[13] = u8x2_to_op<kF16>(r1.z, 2);
+              p[14] = u8x2_to_op<kF16>(r1.w, 0); p[15] = u8x2_to_op<kF16>(r1.w, 2);
+              tmem_st16(dst + 16u * h2, p);
             }
           }
-          if (!(P.debug & 8)) fence_proxy_async_smem();
-          mbar_arrive(&bars->full[stage]);
-          mbar_arrive(&bars->raw_empty[rstage]);
+          if (warp == kEpiWarps) RFK_TRACE(0, 2);
+          tmem_st_wait();
+          tc_fence_before_sync();
+          warp_arrive2(&bars->a_full[gs % A_STAGES], &bars->raw_empty[rstage]);
           if (warp == kEpiWarps) RFK_TRACE(0, 3);
-          if (++stage == STAGES) { stage = 0; phase ^= 1u; }
           if (++rstage == RAW_STAGES) { rstage = 0; rphase ^= 1u; }
         }
       }
@@ -507,59 +537,73 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
   }
   if (warp == WARP_LOAD) {
     // =============================================================== loader: raw query tiles + first-layer weights
-    // The raw ring runs ahead of the operand ring: the TMA load of step s + RAW_STAGES - 1 is in
-    // flight while step s is being converted.
-    int stage = 0, rstage = 0;
-    uint32_t phase = 0, rphase = 0;
+    // Two independent cursors served by one warp.  The raw ring (TMA tensor loads of the uint8 tile)
+    // runs RAW_STAGES ahead of the conversion; the weight ring (cp.async.bulk of the pre-swizzled W1
+    // block) runs B_STAGES ahead of the MMAs -- a stage is refilled as soon as the MMAs of the step
+    // that last used it have completed.  Neither cursor may block the other, so the warp polls both
+    // barriers and sleeps briefly when neither can advance.
     int my_tiles = 0;
     for (int tile = tile0; tile < P.n_tiles; tile += tile_step) ++my_tiles;
     const int total_steps = my_tiles * w * n_kb;
-    // raw cursor (runs ahead)
-    int r_tile = tile0, r_t = t0, r_kb = 0, r_step = 0;
-    auto issue_raw = [&]() {
-      wait_prof<kProf>(&bars->raw_empty[rstage], rphase ^ 1u, prof, PF_LOAD_RAW_EMPTY);
-      RFK_TRACE(1, 1);
-      if (lane == 0) {
-        if (P.debug & 32) {
-          mbar_arrive(&bars->raw_full[rstage]);
-        } else {
-          mbar_arrive_expect_tx(&bars->raw_full[rstage], RAW_STAGE);
-          tma_load_2d(smem + OFF_RAW + rstage * RAW_STAGE, &x_map, r_kb * KB, r_tile * TILE_M, &bars->raw_full[rstage]);
-        }
-      }
-      __syncwarp();
-      if (++rstage == RAW_STAGES) { rstage = 0; rphase ^= 1u; }
-      ++r_step;
-      if (++r_kb == n_kb) {
-        r_kb = 0;
-        if (++r_t == t1) {
-          r_t = t0;
-          r_tile += tile_step;
-        }
-      }
-    };
-    for (int i = 0; i < RAW_STAGES - 1 && r_step < total_steps; ++i) issue_raw();
-    for (int tile = tile0; tile < P.n_tiles; tile += tile_step) {
-      for (int t = t0; t < t1; ++t) {
-        const TrialDev& T = P.trial[t];
+    const int n_atoms = (P.d + ATOM_K - 1) / ATOM_K;
+    int rstage = 0, r_tile = tile0, r_kb = 0, r_t = t0, r_step = 0;
+    uint32_t rphase = 0;
+    int bstage = 0, b_kb = 0, b_t = t0, b_step = 0;
+    uint32_t bphase = 0;
+    uint32_t idle = 0;
+    while (r_step < total_steps || b_step < total_steps) {
+      bool progressed = false;
+      if (b_step < total_steps && __shfl_sync(0xffffffffu, (int)mbar_test(&bars->step_done[bstage], bphase ^ 1u), 0)) {
+        RFK_TRACE(1, 3);
+        const TrialDev& T = P.trial[b_t];
         const uint32_t atom_bytes = (uint32_t)T.h1_pad * 128u;        // one 64-wide K atom of W1
-        const int n_atoms = (P.d + ATOM_K - 1) / ATOM_K;
-        const uint8_t* src = T.w1;
-        for (int kb = 0; kb < n_kb; ++kb) {
-          const uint32_t bytes = atom_bytes * (uint32_t)(n_atoms - 2 * kb < 2 ? n_atoms - 2 * kb : 2);
-          if (r_step < total_steps) issue_raw();
-          wait_prof<kProf>(&bars->empty[stage], phase ^ 1u, prof, PF_LOAD_EMPTY);
-          RFK_TRACE(1, 3);
-          if (lane == 0) {
-            if (P.debug & 1) {
-              mbar_arrive(&bars->full[stage]);
-            } else {
-              mbar_arrive_expect_tx(&bars->full[stage], bytes);
-              bulk_g2s(smem + OFF_B + stage * B_STAGE, src + (size_t)kb * 2 * atom_bytes, bytes, &bars->full[stage]);
-            }
+        const uint32_t bytes = atom_bytes * (uint32_t)(n_atoms - 2 * b_kb < 2 ? n_atoms - 2 * b_kb : 2);
+        if (lane == 0) {
+          if (P.debug & 1) {
+            mbar_arrive(&bars->b_full[bstage]);
+          } else {
+            mbar_arrive_expect_tx(&bars->b_full[bstage], bytes);
+            bulk_g2s(smem + OFF_B + bstage * B_STAGE, T.w1 + (size_t)b_kb * 2 * atom_bytes, bytes, &bars->b_full[bstage]);
           }
-          __syncwarp();
-          if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+        }
+        __syncwarp();
+        if (++bstage == B_STAGES) { bstage = 0; bphase ^= 1u; }
+        ++b_step;
+        if (++b_kb == n_kb) {
+          b_kb = 0;
+          if (++b_t == t1) b_t = t0;
+        }
+        progressed = true;
+      }
+      if (r_step < total_steps && __shfl_sync(0xffffffffu, (int)mbar_test(&bars->raw_empty[rstage], rphase ^ 1u), 0)) {
+        RFK_TRACE(1, 1);
+        if (lane == 0) {
+          if (P.debug & 32) {
+            mbar_arrive(&bars->raw_full[rstage]);
+          } else {
+            mbar_arrive_expect_tx(&bars->raw_full[rstage], RAW_STAGE);
+            tma_load_2d(smem + OFF_RAW + rstage * RAW_STAGE, &x_map, r_kb * KB, r_tile * TILE_M, &bars->raw_full[rstage]);
+          }
+        }
+        __syncwarp();
+        if (++rstage == RAW_STAGES) { rstage = 0; rphase ^= 1u; }
+        ++r_step;
+        if (++r_kb == n_kb) {
+          r_kb = 0;
+          if (++r_t == t1) {
+            r_t = t0;
+            r_tile += tile_step;
+          }
+        }
+        progressed = true;
+      }
+      if (progressed) {
+        idle = 0;
+      } else {
+        __nanosleep(64);
+        if (++idle > (1u << 24)) {          // ~1 s: a pipeline bug must trap, not hang
+          if (lane == 0) printf("rafiki_b200: loader stalled (block %d, raw step %d, weight step %d)\n", blockIdx.x, r_step, b_step);
+          __trap();
         }
       }
     }
@@ -569,7 +613,7 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
     // the layer-2 MMAs of the previous item have completed (so its reload overlaps the previous
     // item's layer-2 epilogue and layer 3).  With a single trial nothing is reloaded.
     int item = 0, n2 = 0;
-    for (int tile = tile0; tile < P.n_tiles; tile += tile_step) {
+    for (int tile = tile0; tile < ((P.debug & 64) ? 0 : P.n_tiles); tile += tile_step) {
       for (int t = t0; t < t1; ++t, ++item) {
         const TrialDev& T = P.trial[t];
         const int buf = item & 1;
@@ -607,14 +651,12 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
   } else if (warp == WARP_MMA) {
     // =============================================================== MMA issuer, layer 1
     // Executed by all 32 lanes in lock step (mbarrier waits included); the *_elect helpers pick
-    // one lane per statement, so there is no divergent region.  Descriptors are a constant upper
-    // word plus (address >> 4) in the lower word.  The probe of the NEXT stage's barrier is
-    // issued before this stage's commit so that its latency hides behind the commit.
-    int stage = 0;
-    uint32_t phase = 0;
-    const uint32_t a_lo0 = desc_lo_sw128(smem_base + OFF_A), b_lo0 = desc_lo_sw128(smem_base + OFF_B);
-    bool next_ready = false;
-    int item = 0;
+    // one lane per statement, so there is no divergent region.  A comes from tensor memory (the
+    // converters' ring, 8 columns per 16-element K step), B from shared memory: the descriptor is a
+    // constant upper word plus (address >> 4) in the lower word.  One commit per step releases both
+    // the weight stage (to the loader) and the A stage (to the converters).
+    const uint32_t b_lo0 = desc_lo_sw128(smem_base + OFF_B);
+    int item = 0, gs = 0;
     for (int tile = tile0; tile < P.n_tiles; tile += tile_step) {
       for (int t = t0; t < t1; ++t, ++item) {
         const TrialDev& T = P.trial[t];
@@ -623,25 +665,24 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
         const uint32_t d_tmem = tmem_base + COL_ACC1 + buf * HMAX;
         wait_prof<kProf>(&bars->acc1_empty[buf], (uint32_t)(((item >> 1) & 1) ^ 1), prof, PF_MMA_ACC1_EMPTY);
         tc_fence_after_sync();
-        for (int kb = 0; kb < n_kb; ++kb) {
-          if (!next_ready) wait_prof<kProf>(&bars->full[stage], phase, prof, PF_MMA_FULL);
+        for (int kb = 0; kb < n_kb; ++kb, ++gs) {
+          const int as = gs % A_STAGES, bs = gs % B_STAGES;
+          wait_prof<kProf>(&bars->b_full[bs], (uint32_t)((gs / B_STAGES) & 1), prof, PF_MMA_W23_FULL);
+          wait_prof<kProf>(&bars->a_full[as], (uint32_t)((gs / A_STAGES) & 1), prof, PF_MMA_FULL);
           RFK_TRACE(2, 1);
           tc_fence_after_sync();
           if (!(P.debug & 4)) {
             // two 64-wide atoms per step; the ragged end of the row may leave the second one short or empty
             const int k16 = (P.d - kb * KB) >> 4;                      // 16-element K steps left in this row
-            const uint32_t a = a_lo0 + (uint32_t)stage * (A_STAGE >> 4);
-            const uint32_t b = b_lo0 + (uint32_t)stage * (B_STAGE >> 4);
-            mma4_f16_ss_elect(d_tmem, desc_from_lo(a), desc_from_lo(b), idesc1, kb != 0, k16 < 4 ? k16 : 4);
+            const uint32_t a = tmem_base + COL_A + (uint32_t)as * (KB / 2);
+            const uint32_t b = b_lo0 + (uint32_t)bs * (B_STAGE >> 4);
+            mma4_f16_ts_elect(d_tmem, a, desc_from_lo(b), idesc1, kb != 0, k16 < 4 ? k16 : 4);
             if (k16 > 4)
-              mma4_f16_ss_elect(d_tmem, desc_from_lo(a + (A_ATOM >> 4)), desc_from_lo(b + (((uint32_t)T.h1_pad * 128u) >> 4)),
-                                idesc1, 1u, k16 - 4 < 4 ? k16 - 4 : 4);
+              mma4_f16_ts_elect(d_tmem, a + 32u, desc_from_lo(b + (((uint32_t)T.h1_pad * 128u) >> 4)), idesc1, 1u,
+                                k16 - 4 < 4 ? k16 - 4 : 4);
           }
           RFK_TRACE(2, 2);
-          const int cur = stage;
-          if (++stage == STAGES) { stage = 0; phase ^= 1u; }
-          next_ready = mbar_test(&bars->full[stage], phase);
-          mma_commit_elect(&bars->empty[cur]);
+          mma_commit_elect(&bars->step_done[bs]);
           if (kb == n_kb - 1) mma_commit_elect(&bars->acc1_full[buf]);
           RFK_TRACE(2, 3);
         }
@@ -663,7 +704,7 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
       }
     };
     int item = 0, n2 = 0;
-    for (int tile = tile0; tile < P.n_tiles; tile += tile_step) {
+    for (int tile = tile0; tile < ((P.debug & 64) ? 0 : P.n_tiles); tile += tile_step) {
       for (int t = t0; t < t1; ++t, ++item) {
         const TrialDev& T = P.trial[t];
         const int buf = item & 1;
@@ -671,15 +712,18 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
           if (w > 1 || n2 == 0) wait_prof<kProf>(&bars->w2_full, (uint32_t)(n2 & 1), prof, PF_MMA_W23_FULL);
           ++n2;
           wait_prof<kProf>(&bars->hid_ready, hid_phase, prof, PF_MMA_HID_L2);
+          RFK_TRACE(4, 1);
           hid_phase ^= 1u;
           tc_fence_after_sync();
-          issue_small_layer(tmem_base + COL_ACC2, w2_lo, ((uint32_t)T.h2_pad * 128u) >> 4,
+          issue_small_layer(tmem_base + COL_ACC1 + (uint32_t)buf * HMAX, w2_lo, ((uint32_t)T.h2_pad * 128u) >> 4,
                             idesc_16bit_f32(kF16, TILE_M, T.h2_pad), T.h1_pad >> 4);
           mma_commit_elect(&bars->acc2_full);
           mma_commit_elect(&bars->w2_free);
+          RFK_TRACE(4, 2);
         }
         if (w > 1 || item < 2) wait_prof<kProf>(&bars->w3_full[buf], (uint32_t)((item >> 1) & 1), prof, PF_MMA_W23_FULL);
         wait_prof<kProf>(&bars->hid_ready, hid_phase, prof, PF_MMA_HID_L3);
+        RFK_TRACE(4, 3);
         hid_phase ^= 1u;
         tc_fence_after_sync();
         const int hl_pad = T.n_hidden == 2 ? T.h2_pad : T.h1_pad;
@@ -687,6 +731,7 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
                           idesc_16bit_f32(kF16, TILE_M, CPAD), hl_pad >> 4);
         mma_commit_elect(&bars->acc3_full);
         mma_commit_elect(&bars->w3_free[buf]);
+        RFK_TRACE(4, 4);
       }
     }
   }
@@ -802,10 +847,10 @@ int fused_forward(rfk_mlp* const* trials, int w, int total_trials, const uint8_t
                   void* ws, size_t ws_bytes, cudaStream_t st) {
   RFK_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0, "fused forward: x must be 16-byte aligned");
   const int d = trials[0]->d;
-  // TMA descriptor of the query batch: uint8 [n, d]; one box = 128 rows x 64 bytes
+  // TMA descriptor of the query batch: uint8 [n, d]; one box = 128 rows x 128 bytes, 128-byte swizzle
   CUtensorMap x_map;
   {
-    const int rc = make_tmap_u8_2d(&x_map, x, (uint64_t)n, (uint64_t)d, (uint64_t)d, TILE_M, KB);
+    const int rc = make_tmap_u8_2d(&x_map, x, (uint64_t)n, (uint64_t)d, (uint64_t)d, TILE_M, KB, true);
     if (rc != RFK_OK) return rc;
   }
   FusedParams P;
@@ -840,7 +885,7 @@ int fused_forward(rfk_mlp* const* trials, int w, int total_trials, const uint8_t
   if (prof_env != nullptr && atoi(prof_env) != 0 && trials[0]->dtype == RFK_F16) {
     // development aid: synchronous, allocates; prints the per-role blocked-cycle breakdown
     long long* dprof = nullptr;
-    const size_t prof_elems = PF_COUNT + 4 * kTraceLen;
+    const size_t prof_elems = PF_COUNT + 5 * kTraceLen;
     RFK_CUDA_TRY(cudaMalloc(&dprof, prof_elems * sizeof(long long)));
     RFK_CUDA_TRY(cudaMemsetAsync(dprof, 0, prof_elems * sizeof(long long), st));
     P.prof = dprof;
@@ -855,8 +900,8 @@ int fused_forward(rfk_mlp* const* trials, int w, int total_trials, const uint8_t
       const char* path = getenv("RFK_FUSED_TRACE_FILE");
       FILE* f = fopen(path ? path : "fused_trace.txt", "w");
       if (f) {
-        static const char* roles[4] = {"conv", "load", "mma", "epi"};
-        for (int r = 0; r < 4; ++r)
+        static const char* roles[5] = {"conv", "load", "mma", "epi", "tail"};
+        for (int r = 0; r < 5; ++r)
           for (int i = 0; i < kTraceLen; ++i) {
             const long long v = hall[PF_COUNT + r * kTraceLen + i];
             if (v != 0) fprintf(f, "%s %d %lld %lld\n", roles[r], i, v >> 4, v & 15);

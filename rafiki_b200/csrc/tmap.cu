@@ -21,7 +21,7 @@ EncodeTiledFn encoder() {
 }  // namespace
 
 int make_tmap_u8_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t pitch,
-                    uint32_t box_rows, uint32_t box_cols) {
+                    uint32_t box_rows, uint32_t box_cols, bool swizzle128) {
   EncodeTiledFn fn = encoder();
   if (fn == nullptr) {
     set_error("cuTensorMapEncodeTiled is not available from this driver");
@@ -32,8 +32,8 @@ int make_tmap_u8_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t 
   const cuuint32_t box[2] = {box_cols, box_rows};
   const cuuint32_t elem[2] = {1, 1};
   const CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void*>(base), dims, strides, box, elem,
-                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                        CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_error("cuTensorMapEncodeTiled failed with CUresult %d (base %p rows %llu cols %llu pitch %llu)", (int)r, base,
               (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)pitch);
