@@ -90,8 +90,7 @@ constexpr int kEpiWarps = 8, kConvWarps = 8;
 constexpr int kEpiThreads = kEpiWarps * 32;                   // 256
 constexpr int kConvThreads = kConvWarps * 32;                 // 256: half a row (64 bytes) per thread per step
 constexpr int kThreads = (kEpiWarps + kConvWarps + 4) * 32;   // 640
-constexpr int WARP_LOAD = kEpiWarps + kConvWarps, WARP_MMA = WARP_LOAD + 1, WARP_PAR = WARP_LOAD + 2,
-              WARP_TAIL = WARP_LOAD + 3;
+constexpr int WARP_LOAD = kEpiWarps + kConvWarps, WARP_MMA = WARP_LOAD + 1 /* and + 2 */, WARP_TAIL = WARP_LOAD + 3;
 constexpr int kRegsEpi = 136, kRegsLight = 56;
 
 constexpr int TMEM_COLS = 512;
@@ -288,7 +287,7 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
       mbar_init(&bars->raw_empty[s], kConvWarps);
     }
     for (int b = 0; b < 2; ++b) {
-      mbar_init(&bars->acc1_full[b], 1);
+      mbar_init(&bars->acc1_full[b], 2);                 // one commit from each layer-1 issuer
       mbar_init(&bars->acc1_empty[b], kEpiWarps);
       mbar_init(&bars->bias_full[b], 1);
       mbar_init(&bars->bias_free[b], kEpiWarps);
@@ -536,126 +535,114 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
     asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsLight));
   }
   if (warp == WARP_LOAD) {
-    // =============================================================== loader: raw query tiles + first-layer weights
-    // Two independent cursors served by one warp.  The raw ring (TMA tensor loads of the uint8 tile)
-    // runs RAW_STAGES ahead of the conversion; the weight ring (cp.async.bulk of the pre-swizzled W1
-    // block) runs B_STAGES ahead of the MMAs -- a stage is refilled as soon as the MMAs of the step
-    // that last used it have completed.  Neither cursor may block the other, so the warp polls both
-    // barriers and sleeps briefly when neither can advance.
+    // =============================================================== loader: weights, raw query tiles, parameters
+    // Per step j: the W1 block of step j (cp.async.bulk of the pre-swizzled block into the B_STAGES-deep
+    // weight ring, as soon as the MMAs of step j - B_STAGES have completed) and the raw uint8 tile
+    // of step j (TMA tensor load into the RAW_STAGES-deep raw ring).  The second wait never blocks in
+    // steady state: the MMAs of step j - 4 completing implies the conversion of step j - 3 is done.
+    // Per-item parameters (biases, W3: double buffered by item parity; W2: one buffer, released
+    // as soon as the layer-2 MMAs of the previous item have completed) ride along as a third,
+    // non-blocking cursor that is polled once per step; with a single trial nothing is reloaded.
     int my_tiles = 0;
     for (int tile = tile0; tile < P.n_tiles; tile += tile_step) ++my_tiles;
-    const int total_steps = my_tiles * w * n_kb;
+    const int total_items = (P.debug & 64) ? 0 : my_tiles * w;
     const int n_atoms = (P.d + ATOM_K - 1) / ATOM_K;
-    int rstage = 0, r_tile = tile0, r_kb = 0, r_t = t0, r_step = 0;
-    uint32_t rphase = 0;
-    int bstage = 0, b_kb = 0, b_t = t0, b_step = 0;
-    uint32_t bphase = 0;
-    uint32_t idle = 0;
-    while (r_step < total_steps || b_step < total_steps) {
-      bool progressed = false;
-      if (b_step < total_steps && __shfl_sync(0xffffffffu, (int)mbar_test(&bars->step_done[bstage], bphase ^ 1u), 0)) {
-        RFK_TRACE(1, 3);
-        const TrialDev& T = P.trial[b_t];
-        const uint32_t atom_bytes = (uint32_t)T.h1_pad * 128u;        // one 64-wide K atom of W1
-        const uint32_t bytes = atom_bytes * (uint32_t)(n_atoms - 2 * b_kb < 2 ? n_atoms - 2 * b_kb : 2);
-        if (lane == 0) {
-          if (P.debug & 1) {
-            mbar_arrive(&bars->b_full[bstage]);
-          } else {
-            mbar_arrive_expect_tx(&bars->b_full[bstage], bytes);
-            bulk_g2s(smem + OFF_B + bstage * B_STAGE, T.w1 + (size_t)b_kb * 2 * atom_bytes, bytes, &bars->b_full[bstage]);
-          }
-        }
-        __syncwarp();
-        if (++bstage == B_STAGES) { bstage = 0; bphase ^= 1u; }
-        ++b_step;
-        if (++b_kb == n_kb) {
-          b_kb = 0;
-          if (++b_t == t1) b_t = t0;
-        }
-        progressed = true;
+    int p_item = 0, p_t = t0, p_sub = 0, n2 = 0;
+    auto param_poll = [&](bool blocking) {
+      // at most one action per call; returns when the cursor cannot advance (non-blocking mode)
+      if (p_item >= total_items) return;
+      const TrialDev& T = P.trial[p_t];
+      const int buf = p_item & 1;
+      const uint32_t par_free2 = (uint32_t)(((p_item >> 1) & 1) ^ 1);
+      if (p_sub < 2 && !(w > 1 || p_item < 2)) p_sub = 2;
+      if (p_sub == 0) {
+        if (blocking) mbar_wait(&bars->bias_free[buf], par_free2);
+        else if (!mbar_test(&bars->bias_free[buf], par_free2)) return;
+        bulk_g2s_expect_elect(smem + OFF_BIAS + buf * BIAS_BYTES, T.bias, BIAS_BYTES, &bars->bias_full[buf]);
+        p_sub = 1;
+        return;
       }
-      if (r_step < total_steps && __shfl_sync(0xffffffffu, (int)mbar_test(&bars->raw_empty[rstage], rphase ^ 1u), 0)) {
-        RFK_TRACE(1, 1);
-        if (lane == 0) {
-          if (P.debug & 32) {
-            mbar_arrive(&bars->raw_full[rstage]);
-          } else {
-            mbar_arrive_expect_tx(&bars->raw_full[rstage], RAW_STAGE);
-            tma_load_2d(smem + OFF_RAW + rstage * RAW_STAGE, &x_map, r_kb * KB, r_tile * TILE_M, &bars->raw_full[rstage]);
-          }
-        }
-        __syncwarp();
-        if (++rstage == RAW_STAGES) { rstage = 0; rphase ^= 1u; }
-        ++r_step;
-        if (++r_kb == n_kb) {
-          r_kb = 0;
-          if (++r_t == t1) {
-            r_t = t0;
-            r_tile += tile_step;
-          }
-        }
-        progressed = true;
+      if (p_sub == 1) {
+        if (blocking) mbar_wait(&bars->w3_free[buf], par_free2);
+        else if (!mbar_test(&bars->w3_free[buf], par_free2)) return;
+        const int hl_pad = T.n_hidden == 2 ? T.h2_pad : T.h1_pad;
+        const uint32_t w3_bytes = (uint32_t)((hl_pad + 63) / 64) * CPAD * 128u;
+        bulk_g2s_expect_elect(smem + OFF_W3 + buf * W3_BYTES, T.w3, w3_bytes, &bars->w3_full[buf]);
+        p_sub = 2;
+        return;
       }
-      if (progressed) {
-        idle = 0;
-      } else {
-        __nanosleep(64);
-        if (++idle > (1u << 24)) {          // ~1 s: a pipeline bug must trap, not hang
-          if (lane == 0) printf("rafiki_b200: loader stalled (block %d, raw step %d, weight step %d)\n", blockIdx.x, r_step, b_step);
+      if (T.n_hidden == 2 && (w > 1 || n2 == 0)) {
+        if (blocking) mbar_wait(&bars->w2_free, (uint32_t)((n2 & 1) ^ 1));
+        else if (!mbar_test(&bars->w2_free, (uint32_t)((n2 & 1) ^ 1))) return;
+        const uint32_t w2_bytes = (uint32_t)((T.h1_pad + 63) / 64) * (uint32_t)T.h2_pad * 128u;
+        bulk_g2s_expect_elect(smem + OFF_W2, T.w2, w2_bytes, &bars->w2_full);
+      }
+      if (T.n_hidden == 2) ++n2;
+      ++p_item;
+      p_sub = 0;
+      if (++p_t == t1) p_t = t0;
+    };
+    // Waiting for a ring slot must not starve the parameter cursor (the MMAs the slot waits for may
+    // themselves be waiting, through the epilogue, for parameters): poll it between bounded waits.
+    auto wait_serving = [&](uint64_t* bar, uint32_t parity) {
+      if (mbar_try_wait(bar, parity)) return;
+      uint32_t spins = 0;
+      while (!mbar_try_wait_hint(bar, parity, 200u)) {
+        param_poll(false);
+        if (++spins > (1u << 24)) {
+          if (lane == 0) printf("rafiki_b200: loader wait timed out (block %d)\n", blockIdx.x);
           __trap();
         }
       }
-    }
-  } else if (warp == WARP_PAR) {
-    // =============================================================== per-trial parameter loader
-    // biases and W3 are double buffered by item parity; W2 has one buffer, released as soon as
-    // the layer-2 MMAs of the previous item have completed (so its reload overlaps the previous
-    // item's layer-2 epilogue and layer 3).  With a single trial nothing is reloaded.
-    int item = 0, n2 = 0;
-    for (int tile = tile0; tile < ((P.debug & 64) ? 0 : P.n_tiles); tile += tile_step) {
-      for (int t = t0; t < t1; ++t, ++item) {
+    };
+    // the parameters of the first two items have free buffers: load them before anything else
+    for (int i = 0; i < 6; ++i) param_poll(false);
+    int bstage = 0, rstage = 0;
+    uint32_t bphase = 0, rphase = 0;
+    for (int tile = tile0; tile < P.n_tiles; tile += tile_step) {
+      for (int t = t0; t < t1; ++t) {
         const TrialDev& T = P.trial[t];
-        const int buf = item & 1;
-        const uint32_t par_free2 = (uint32_t)(((item >> 1) & 1) ^ 1);
-        if (w > 1 || item < 2) {
-          wait_prof<kProf>(&bars->bias_free[buf], par_free2, prof, PF_PAR_BIAS_FREE);
-          if (lane == 0) {
-            mbar_arrive_expect_tx(&bars->bias_full[buf], BIAS_BYTES);
-            bulk_g2s(smem + OFF_BIAS + buf * BIAS_BYTES, T.bias, BIAS_BYTES, &bars->bias_full[buf]);
-          }
-          __syncwarp();
-          wait_prof<kProf>(&bars->w3_free[buf], par_free2, prof, PF_PAR_W23_FREE);
-          const int hl_pad = T.n_hidden == 2 ? T.h2_pad : T.h1_pad;
-          const uint32_t w3_bytes = (uint32_t)((hl_pad + 63) / 64) * CPAD * 128u;
-          if (lane == 0) {
-            mbar_arrive_expect_tx(&bars->w3_full[buf], w3_bytes);
-            bulk_g2s(smem + OFF_W3 + buf * W3_BYTES, T.w3, w3_bytes, &bars->w3_full[buf]);
-          }
-          __syncwarp();
-        }
-        if (T.n_hidden == 2) {
-          if (w > 1 || n2 == 0) {
-            wait_prof<kProf>(&bars->w2_free, (uint32_t)((n2 & 1) ^ 1), prof, PF_PAR_W23_FREE);
-            const uint32_t w2_bytes = (uint32_t)((T.h1_pad + 63) / 64) * (uint32_t)T.h2_pad * 128u;
-            if (lane == 0) {
-              mbar_arrive_expect_tx(&bars->w2_full, w2_bytes);
-              bulk_g2s(smem + OFF_W2, T.w2, w2_bytes, &bars->w2_full);
-            }
-            __syncwarp();
-          }
-          ++n2;
+        const uint32_t atom_bytes = (uint32_t)T.h1_pad * 128u;        // one 64-wide K atom of W1
+        const uint8_t* src = T.w1;
+        for (int kb = 0; kb < n_kb; ++kb) {
+          const uint32_t bytes = atom_bytes * (uint32_t)(n_atoms - 2 * kb < 2 ? n_atoms - 2 * kb : 2);
+          wait_serving(&bars->step_done[bstage], bphase ^ 1u);
+          RFK_TRACE(1, 3);
+          if (P.debug & 1)
+            mbar_arrive_elect(&bars->b_full[bstage]);
+          else
+            bulk_g2s_expect_elect(smem + OFF_B + bstage * B_STAGE, src + (size_t)kb * 2 * atom_bytes, bytes, &bars->b_full[bstage]);
+          wait_serving(&bars->raw_empty[rstage], rphase ^ 1u);
+          RFK_TRACE(1, 1);
+          if (P.debug & 32)
+            mbar_arrive_elect(&bars->raw_full[rstage]);
+          else
+            tma_load_2d_expect_elect(smem + OFF_RAW + rstage * RAW_STAGE, &x_map, kb * KB, tile * TILE_M, RAW_STAGE,
+                                     &bars->raw_full[rstage]);
+          if (++bstage == B_STAGES) { bstage = 0; bphase ^= 1u; }
+          if (++rstage == RAW_STAGES) { rstage = 0; rphase ^= 1u; }
+          param_poll(false);
         }
       }
     }
-  } else if (warp == WARP_MMA) {
-    // =============================================================== MMA issuer, layer 1
+    while (p_item < total_items) param_poll(true);
+  } else if (warp == WARP_MMA || warp == WARP_MMA + 1) {
+    // =============================================================== MMA issuers, layer 1 (two warps)
     // Executed by all 32 lanes in lock step (mbarrier waits included); the *_elect helpers pick
     // one lane per statement, so there is no divergent region.  A comes from tensor memory (the
     // converters' ring, 8 columns per 16-element K step), B from shared memory: the descriptor is a
     // constant upper word plus (address >> 4) in the lower word.  One commit per step releases both
     // the weight stage (to the loader) and the A stage (to the converters).
+    // Issuing eight MMAs costs about as many cycles as executing them (operands travel through
+    // uniform registers), so one warp alone leaves the tensor pipe idle while it commits and polls
+    // the next step's barriers.  Two warps take alternate steps: while one issues, the other commits
+    // its previous step and waits for its next operands; a named-barrier token (ids 2 and 3) passes
+    // the turn so that the MMAs enter the pipe in step order.
+    const int me = warp - WARP_MMA;
     const uint32_t b_lo0 = desc_lo_sw128(smem_base + OFF_B);
+    int my_tiles = 0;
+    for (int tile = tile0; tile < P.n_tiles; tile += tile_step) ++my_tiles;
+    const int total_steps = my_tiles * w * n_kb;
     int item = 0, gs = 0;
     for (int tile = tile0; tile < P.n_tiles; tile += tile_step) {
       for (int t = t0; t < t1; ++t, ++item) {
@@ -663,13 +650,23 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
         const int buf = item & 1;
         const uint32_t idesc1 = idesc_16bit_f32(kF16, TILE_M, T.h1_pad);
         const uint32_t d_tmem = tmem_base + COL_ACC1 + buf * HMAX;
-        wait_prof<kProf>(&bars->acc1_empty[buf], (uint32_t)(((item >> 1) & 1) ^ 1), prof, PF_MMA_ACC1_EMPTY);
-        tc_fence_after_sync();
+        bool acc_ready = false;
         for (int kb = 0; kb < n_kb; ++kb, ++gs) {
+          if ((gs & 1) != me) continue;
+          if (!acc_ready) {
+            wait_prof<kProf>(&bars->acc1_empty[buf], (uint32_t)(((item >> 1) & 1) ^ 1), prof, PF_MMA_ACC1_EMPTY);
+            acc_ready = true;
+          }
           const int as = gs % A_STAGES, bs = gs % B_STAGES;
           wait_prof<kProf>(&bars->b_full[bs], (uint32_t)((gs / B_STAGES) & 1), prof, PF_MMA_W23_FULL);
           wait_prof<kProf>(&bars->a_full[as], (uint32_t)((gs / A_STAGES) & 1), prof, PF_MMA_FULL);
-          RFK_TRACE(2, 1);
+          if (gs > 0) {                     // my turn: the other warp has issued step gs - 1
+            if (me == 0)
+              asm volatile("bar.sync 2, 64;" ::: "memory");
+            else
+              asm volatile("bar.sync 3, 64;" ::: "memory");
+          }
+          if (me == 0) RFK_TRACE(2, 1);
           tc_fence_after_sync();
           if (!(P.debug & 4)) {
             // two 64-wide atoms per step; the ragged end of the row may leave the second one short or empty
@@ -681,11 +678,19 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
               mma4_f16_ts_elect(d_tmem, a + 32u, desc_from_lo(b + (((uint32_t)T.h1_pad * 128u) >> 4)), idesc1, 1u,
                                 k16 - 4 < 4 ? k16 - 4 : 4);
           }
-          RFK_TRACE(2, 2);
+          if (me == 0) RFK_TRACE(2, 2);
+          tc_fence_before_sync();
+          if (gs + 1 < total_steps) {       // pass the turn
+            if (me == 0)
+              asm volatile("bar.arrive 3, 64;" ::: "memory");
+            else
+              asm volatile("bar.arrive 2, 64;" ::: "memory");
+          }
           mma_commit_elect(&bars->step_done[bs]);
-          if (kb == n_kb - 1) mma_commit_elect(&bars->acc1_full[buf]);
-          RFK_TRACE(2, 3);
+          if (me == 0) RFK_TRACE(2, 3);
         }
+        // completes once the MMAs this warp issued for the item are done (at once if it had no step)
+        mma_commit_elect(&bars->acc1_full[buf]);
       }
     }
   } else if (warp == WARP_TAIL) {
@@ -736,7 +741,7 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
     }
   }
   if (kProf && P.prof != nullptr && lane == 0 &&
-      (warp == 0 || warp == kEpiWarps || warp == WARP_LOAD || warp == WARP_MMA || warp == WARP_PAR || warp == WARP_TAIL)) {
+      (warp == 0 || warp == kEpiWarps || warp == WARP_LOAD || warp == WARP_MMA || warp == WARP_TAIL)) {
     const long long total = clock64() - t_start;
     if (warp == 0) prof[PF_EPI_TOTAL] = total;
     if (warp == kEpiWarps) prof[PF_CONV_TOTAL] = total;
