@@ -146,9 +146,18 @@ __device__ __forceinline__ uint32_t u8x2_to_f16x2(uint32_t word, int e0) {
   asm("sub.rn.f16x2 %0, %1, %2;" : "=r"(r) : "r"(biased), "r"(0x64006400u));
   return r;
 }
+// uint8 -> fp16 SUBNORMAL: the 16-bit pattern 0x00bb is the half-precision value b * 2^-24 (no implicit
+// bit), so zero-extending the bytes IS the conversion -- one PRMT per pair and no arithmetic.  The
+// tensor core multiplies subnormal operands exactly; the layer-1 epilogue scales the fp32
+// accumulator back by 2^24 inside the FFMA that adds the bias (a power of two: bit-identical to
+// converting to b itself).
+__device__ __forceinline__ uint32_t u8x2_to_f16x2_subnormal(uint32_t word, int e0) {
+  return __byte_perm(word, 0u, 0x4040u | (uint32_t)e0 | ((uint32_t)(e0 + 1) << 8));
+}
+constexpr float kSubnormalScale = 16777216.0f;   // 2^24
 template <bool kF16>
 __device__ __forceinline__ uint32_t u8x2_to_op(uint32_t word, int e0) {
-  return kF16 ? u8x2_to_f16x2(word, e0) : u8x2_to_bf16x2(word, e0);
+  return kF16 ? u8x2_to_f16x2_subnormal(word, e0) : u8x2_to_bf16x2(word, e0);
 }
 
 // relu(lo), relu(hi) -> packed 16-bit operand pair (lo in the low half), one instruction;
@@ -176,14 +185,17 @@ __device__ __forceinline__ void sts_u4(uint32_t addr, uint4 v) {
 // 16 accumulator columns of one row -> bias + ReLU -> 16-bit pairs -> 8 columns of the hidden
 // activations in tensor memory (element k of the row lives in the low/high half of column k/2)
 template <bool kF16>
-__device__ __forceinline__ void hidden_store16(const uint32_t (&v)[16], int c, const float* bias, uint32_t hid_row_addr) {
+__device__ __forceinline__ void hidden_store16(const uint32_t (&v)[16], int c, const float* bias, float scale,
+                                               uint32_t hid_row_addr) {
   const float4* b4 = reinterpret_cast<const float4*>(bias + c);
   uint32_t p[8];
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
     const float4 bb = b4[j];
-    p[2 * j] = relu_pack_x2<kF16>(__uint_as_float(v[4 * j + 0]) + bb.x, __uint_as_float(v[4 * j + 1]) + bb.y);
-    p[2 * j + 1] = relu_pack_x2<kF16>(__uint_as_float(v[4 * j + 2]) + bb.z, __uint_as_float(v[4 * j + 3]) + bb.w);
+    p[2 * j] = relu_pack_x2<kF16>(fmaf(__uint_as_float(v[4 * j + 0]), scale, bb.x),
+                                  fmaf(__uint_as_float(v[4 * j + 1]), scale, bb.y));
+    p[2 * j + 1] = relu_pack_x2<kF16>(fmaf(__uint_as_float(v[4 * j + 2]), scale, bb.z),
+                                      fmaf(__uint_as_float(v[4 * j + 3]), scale, bb.w));
   }
   tmem_st8(hid_row_addr + (uint32_t)(c >> 1), p);
 }
@@ -194,7 +206,7 @@ __device__ __forceinline__ void hidden_store16(const uint32_t (&v)[16], int c, c
 // four buffers were measured to spill under the 96-register launch bound).
 template <bool kF16>
 __device__ __forceinline__ void epilogue_hidden(uint32_t tmem_row_addr, int c_begin, int c_end, const float* bias,
-                                                uint32_t hid_row_addr) {
+                                                float scale, uint32_t hid_row_addr) {
   if (c_begin < c_end) {
     uint32_t va[16], vb[16];
     tmem_ld16(tmem_row_addr + (uint32_t)c_begin, va);
@@ -202,11 +214,11 @@ __device__ __forceinline__ void epilogue_hidden(uint32_t tmem_row_addr, int c_be
       tmem_ld_wait();
       const bool more_b = c + 16 < c_end;
       if (more_b) tmem_ld16(tmem_row_addr + (uint32_t)c + 16u, vb);
-      hidden_store16<kF16>(va, c, bias, hid_row_addr);
+      hidden_store16<kF16>(va, c, bias, scale, hid_row_addr);
       if (more_b) {
         tmem_ld_wait();
         if (c + 32 < c_end) tmem_ld16(tmem_row_addr + (uint32_t)c + 32u, va);
-        hidden_store16<kF16>(vb, c + 16, bias, hid_row_addr);
+        hidden_store16<kF16>(vb, c + 16, bias, scale, hid_row_addr);
       }
     }
   }
@@ -434,7 +446,7 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
         {
           const int split = T.h1_pad < 64 ? T.h1_pad : 64;
           epilogue_hidden<kF16>(lane_addr + COL_ACC1 + buf * HMAX, half ? split : 0, half ? T.h1_pad : split, bias,
-                                hid_row_addr);
+                                kF16 ? kSubnormalScale : 1.0f, hid_row_addr);
         }
         tc_fence_before_sync();
         // two-hidden-layer items keep the accumulator: layer 2 accumulates into it (see below)
@@ -454,7 +466,7 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
           const int split = T.h2_pad < 64 ? T.h2_pad : 64;
           // layer 2 accumulated into this item's (drained) layer-1 buffer
           epilogue_hidden<kF16>(lane_addr + COL_ACC1 + buf * HMAX, half ? split : 0, half ? T.h2_pad : split, bias + HMAX,
-                                hid_row_addr);
+                                1.0f, hid_row_addr);
           tc_fence_before_sync();
           warp_arrive2(&bars->acc1_empty[buf], &bars->hid_ready);
           if (warp == 0) RFK_TRACE(3, 4);
