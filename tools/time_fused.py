@@ -19,7 +19,7 @@ def main():
             ens.forward(xs[i % 4], out=out)
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        iters = 20
+        iters = int(os.environ.get('RFK_ITERS', '20'))
         e0.record()
         for i in range(iters):
             ens.forward(xs[i % 4], out=out)
