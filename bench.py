@@ -74,37 +74,66 @@ def make_workload(wl, rng_seed=0, n_batches=None):
 
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
+    """SM clock and throttle reasons sampled during the timed region: NVML every 5 ms when the bindings
+    load (a timed region is tens of milliseconds), else nvidia-smi every 200 ms."""
     QUERY = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
              'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+    NAMES = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+    NVML_BITS = [0x8, 0x40, 0x20, 0x4]      # same order as NAMES (nvmlClocksThrottleReason*)
 
     def __init__(self, index):
         super().__init__(daemon=True)
         self.index = index
-        self.samples = []
+        self.samples = []          # (sm_mhz, sm_max_mhz, [bool per NAMES])
         self._halt = threading.Event()
+        self._nvml = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            try:
+                pr = torch.cuda.get_device_properties(index)
+                bus = '%08x:%02x:%02x.0' % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+                self._h = pynvml.nvmlDeviceGetHandleByPciBusId(bus.encode())
+            except Exception:
+                self._h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self._max = pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM)
+            self._nvml = pynvml
+        except Exception:
+            self._nvml = None
+
+    def _sample_nvml(self):
+        n = self._nvml
+        sm = n.nvmlDeviceGetClockInfo(self._h, n.NVML_CLOCK_SM)
+        bits = n.nvmlDeviceGetCurrentClocksThrottleReasons(self._h)
+        self.samples.append((float(sm), float(self._max), [bool(bits & b) for b in self.NVML_BITS]))
+
+    def _sample_smi(self):
+        out = subprocess.run(['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.QUERY,
+                              '--format=csv,noheader,nounits'], capture_output=True, text=True, timeout=5)
+        parts = [x.strip() for x in out.stdout.strip().split(',')]
+        if len(parts) >= 6 and parts[0].replace('.', '', 1).isdigit():
+            self.samples.append((float(parts[0]), float(parts[1]) if parts[1].replace('.', '', 1).isdigit() else None,
+                                 [parts[2 + i].lower().startswith('active') for i in range(4)]))
 
     def run(self):
         while not self._halt.is_set():
             try:
-                out = subprocess.run(['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.QUERY,
-                                      '--format=csv,noheader,nounits'], capture_output=True, text=True, timeout=5)
-                parts = [x.strip() for x in out.stdout.strip().split(',')]
-                if len(parts) >= 6:
-                    self.samples.append(parts)
+                if self._nvml is not None:
+                    self._sample_nvml()
+                else:
+                    self._sample_smi()
             except Exception:
                 pass
-            self._halt.wait(0.2)
+            self._halt.wait(0.005 if self._nvml is not None else 0.2)
 
     def stop(self):
         self._halt.set()
         self.join(3)
-        sm = [float(s[0]) for s in self.samples if s[0].replace('.', '', 1).isdigit()]
-        mx = [float(s[1]) for s in self.samples if s[1].replace('.', '', 1).isdigit()]
-        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
-        reasons = [n for i, n in enumerate(names) if any(s[2 + i].lower().startswith('active') for s in self.samples)]
+        sm = [s[0] for s in self.samples]
+        mx = [s[1] for s in self.samples if s[1] is not None]
+        reasons = [n for i, n in enumerate(self.NAMES) if any(s[2][i] for s in self.samples)]
         return {'sm_mhz': statistics.median(sm) if sm else None, 'sm_max_mhz': max(mx) if mx else None,
-                'reasons': reasons, 'samples': len(self.samples)}
+                'reasons': reasons, 'samples': len(self.samples), 'source': 'nvml' if self._nvml is not None else 'nvidia-smi'}
 
 
 def cpu_oracle_rate(params, batch, sample, repeats, threads):
@@ -197,7 +226,7 @@ def run_latency_sweep(args, wl, ens, xs, out, params, rank):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
-    ap.add_argument('--steps', type=int, default=200)
+    ap.add_argument('--steps', type=int, default=2000)
     ap.add_argument('--warmup', type=int, default=10)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--workload', default='c3', choices=sorted(WORKLOADS))
