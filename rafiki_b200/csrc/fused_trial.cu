@@ -47,8 +47,6 @@
 // bf16 (RFK_BF16); accumulation is fp32 in TMEM either way.
 #include <stdlib.h>
 
-#include <atomic>
-
 #include "pack.cuh"
 #include "rfk_internal.cuh"
 #include "sm100.cuh"
@@ -125,10 +123,6 @@ struct FusedParams {
   long long* prof;   // development only (RFK_FUSED_PROF): PF_COUNT counters, summed over CTAs
   long long* trace;  // development only (RFK_FUSED_PROF=2): block 0 event timestamps, [5 roles][kTraceLen]
   int split;         // 1: one (tile, trial) item per CTA, per-trial probabilities to out[t][n][C] (small batches)
-  int balanced;      // 1: CTAs take equal ranges of (tile, trial) items; a tile may straddle CTAs (see the kernel)
-  unsigned epoch;    // balanced: value a contribution flag must hold to count for THIS launch
-  float* scratch;    // balanced: [grid][W][128][C] per-trial probabilities of straddling tiles
-  unsigned* flags;   // balanced: [grid][W]
   int debug;         // development only (RFK_FUSED_DEBUG): 1 skip W1 copies, 2 skip conversion, 4 skip layer-1 MMAs
 };
 
@@ -341,32 +335,14 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
   constexpr uint32_t tmem_base = 0u;
 
   const int n_kb = P.n_kb;
-  // Work assignment: every CTA takes one contiguous range of (tile, trial) items, tile-major, so
-  // the trials of a tile run back to back (the tile stays hot in L2, the ensemble sum in registers).
-  //  * default: whole tiles, n_tiles / grid each (+-1).
-  //  * balanced (needs caller scratch): items / grid each (+-1) -- 512 tiles over 148 SMs would
-  //    otherwise leave the SMs with three tiles idle while the others run their fourth.  A tile may
-  //    then straddle CTAs: the CTA that runs trial 0 of a tile OWNS it; the others write the
-  //    probabilities of their trials to scratch[owner][t] and raise flags[owner][t]; the owner, when
-  //    it reaches the end of its range, adds them in trial order -- the same float64 sum as if it
-  //    had run them itself.  Contributions are the first items of a range and the owner waits at the
-  //    end of its own, so the wait is satisfied long before it starts (all CTAs are co-resident).
-  //  * split (small batches): CTA b is exactly item b; per-trial probabilities go to out[t][n][C]
-  //    and kernel 3 averages them.
-  const int W = P.w;
-  const long long all_items = (long long)P.n_tiles * W;
-  int item_begin, item_end;
-  if (P.split) {
-    item_begin = (int)blockIdx.x;
-    item_end = item_begin + 1;
-  } else if (P.balanced) {
-    item_begin = (int)(all_items * blockIdx.x / gridDim.x);
-    item_end = (int)(all_items * (blockIdx.x + 1) / gridDim.x);
-  } else {
-    item_begin = (int)((long long)P.n_tiles * blockIdx.x / gridDim.x) * W;
-    item_end = (int)((long long)P.n_tiles * (blockIdx.x + 1) / gridDim.x) * W;
-  }
-  const int n_items = item_end - item_begin;
+  // Work assignment.  Normal: CTA b takes tiles b, b + grid, ... and runs all trials of a tile back
+  // to back.  Split (small batches): CTA b is exactly one item, tile b / W, trial b % W, so that the
+  // trials of a tile run on different SMs at the same time; kernel 3 then averages the W outputs.
+  const int tile0 = P.split ? (int)blockIdx.x / P.w : (int)blockIdx.x;
+  const int tile_step = P.split ? P.n_tiles : (int)gridDim.x;
+  const int t0 = P.split ? (int)blockIdx.x % P.w : 0;
+  const int t1 = P.split ? t0 + 1 : P.w;
+  const int w = t1 - t0;                       // trials this CTA runs per tile
   const uint32_t smem_base = smem_u32(smem);
 
   if (warp < kEpiWarps) {
@@ -386,19 +362,7 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
     // a one-hidden-layer item i may overwrite acc3 as soon as its hidden tile is published.
     uint32_t v3[16];
     bool have_prev = false;
-    int prev_it = 0, prev_buf = 0;
-    // the 128 x C floats staged in shared memory -> global memory as 16-byte stores (the
-    // destination may be peer memory across NVLink, where 4-byte stores would waste most of every packet)
-    auto copy_staged = [&](float* dst, int valid) {
-      const float* stage = reinterpret_cast<const float*>(smem + OFF_OUT);
-      if ((reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
-        const int nvec = valid >> 2;
-        for (int i = row; i < nvec; i += 128) reinterpret_cast<float4*>(dst)[i] = reinterpret_cast<const float4*>(stage)[i];
-        for (int i = (nvec << 2) + row; i < valid; i += 128) dst[i] = stage[i];
-      } else {
-        for (int i = row; i < valid; i += 128) dst[i] = stage[i];
-      }
-    };
+    int prev_tile = 0, prev_t = 0, prev_buf = 0;
     auto finish_prev = [&]() {
       // half 0: logits (v3) + bias -> softmax -> running ensemble sum; store the mean after the last trial
       const float* pbias = reinterpret_cast<const float*>(smem + OFF_BIAS + prev_buf * BIAS_BYTES);
@@ -419,73 +383,36 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
         const float inv = 1.0f / sum;
         warp_arrive(&bars->bias_free[prev_buf]);
 #pragma unroll
-        for (int j = 0; j < CPAD; ++j) z[j] *= inv;
+        for (int j = 0; j < CPAD; ++j) acc[j] += (double)(z[j] * inv);
         if (warp == 0) RFK_TRACE(3, 6);
-        const int C = P.n_classes;
-        const int ptile = prev_it / W, pt = prev_it - ptile * W;
-        float* stage = reinterpret_cast<float*>(smem + OFF_OUT);
-        const long long first = (long long)ptile * TILE_M;
-        const long long rows = P.n - first < TILE_M ? P.n - first : TILE_M;
-        if (P.split || ptile * W < item_begin) {
-          // this trial's probabilities leave the CTA: split mode writes out[t][n][C]; in balanced mode
-          // trial 0 of the tile ran on another CTA (the owner), which will add them to its sum
+        if (prev_t == t1 - 1) {
+          // the tile's ensemble mean: float64 sum in trial order, one division, one rounding.  The
+          // 128 rows of a tile are one contiguous block of the output, so they are staged in shared
+          // memory and leave as 16-byte stores (the output may be peer memory across NVLink, where
+          // 4-byte stores would waste most of every packet).
+          const int C = P.n_classes;
+          float* stage = reinterpret_cast<float*>(smem + OFF_OUT);
 #pragma unroll
           for (int j = 0; j < CPAD; ++j)
-            if (j < C) stage[row * C + j] = z[j];
+            if (j < C) stage[row * C + j] = (float)(acc[j] / (double)(P.split ? 1 : P.total_trials));
+#pragma unroll
+          for (int j = 0; j < CPAD; ++j) acc[j] = 0.0;
           asm volatile("bar.sync 1, 128;" ::: "memory");           // the four softmax warps
-          if (P.split) {
-            copy_staged(P.out + (long long)pt * P.n * C + first * C, (int)rows * C);
-            asm volatile("bar.sync 1, 128;" ::: "memory");         // staging buffer free again
-          } else {
-            // owner = the CTA whose range holds item (ptile, 0)
-            const long long head = (long long)ptile * W;
-            int owner = (int)(head * gridDim.x / all_items);
-            while ((long long)(all_items * (owner + 1) / gridDim.x) <= head) ++owner;
-            while ((long long)(all_items * owner / gridDim.x) > head) --owner;
-            copy_staged(P.scratch + ((size_t)owner * W + pt) * (size_t)(TILE_M * C), TILE_M * C);
-            __threadfence();
-            asm volatile("bar.sync 1, 128;" ::: "memory");         // all rows written and fenced; staging free
-            if (row == 0)
-              asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(P.flags + (size_t)owner * W + pt), "r"(P.epoch) : "memory");
-          }
-        } else {
-#pragma unroll
-          for (int j = 0; j < CPAD; ++j) acc[j] += (double)z[j];
-          if (pt == W - 1 || prev_it == item_end - 1) {
-            if (pt != W - 1) {
-              // the tile continues on other CTAs: wait for their contributions and add them in trial order
-              if (row == 0) {
-                for (int tt = pt + 1; tt < W; ++tt) {
-                  const unsigned* f = P.flags + (size_t)blockIdx.x * W + tt;
-                  unsigned v, spins = 0;
-                  do {
-                    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
-                    if (v != P.epoch && ++spins > (1u << 26)) {
-                      printf("rafiki_b200: contribution (block %d, trial %d) never arrived\n", blockIdx.x, tt);
-                      __trap();
-                    }
-                  } while (v != P.epoch);
-                }
-              }
-              asm volatile("bar.sync 1, 128;" ::: "memory");
-              for (int tt = pt + 1; tt < W; ++tt) {
-                const float* src = P.scratch + ((size_t)blockIdx.x * W + tt) * (size_t)(TILE_M * C) + row * C;
-#pragma unroll
-                for (int j = 0; j < CPAD; ++j)
-                  if (j < C) acc[j] += (double)__ldcg(src + j);
-              }
+          {
+            const long long first = (long long)prev_tile * TILE_M;
+            const long long rows = P.n - first < TILE_M ? P.n - first : TILE_M;
+            const int valid = (int)rows * C;                        // floats of this tile that exist
+            float* o = P.out + (P.split ? (long long)t0 * P.n * C : 0ll) + first * C;
+            if ((reinterpret_cast<uintptr_t>(o) & 15) == 0) {
+              const int nvec = valid >> 2;
+              for (int i = row; i < nvec; i += 128)
+                reinterpret_cast<float4*>(o)[i] = reinterpret_cast<const float4*>(stage)[i];
+              for (int i = (nvec << 2) + row; i < valid; i += 128) o[i] = stage[i];
+            } else {
+              for (int i = row; i < valid; i += 128) o[i] = stage[i];
             }
-            // the tile's ensemble mean: float64 sum in trial order, one division, one rounding.  The
-            // 128 rows of a tile are one contiguous block of the output: staged, then 16-byte stores.
-#pragma unroll
-            for (int j = 0; j < CPAD; ++j)
-              if (j < C) stage[row * C + j] = (float)(acc[j] / (double)P.total_trials);
-#pragma unroll
-            for (int j = 0; j < CPAD; ++j) acc[j] = 0.0;
-            asm volatile("bar.sync 1, 128;" ::: "memory");         // the four softmax warps
-            copy_staged(P.out + first * C, (int)rows * C);
-            asm volatile("bar.sync 1, 128;" ::: "memory");         // staging buffer free again
           }
+          asm volatile("bar.sync 1, 128;" ::: "memory");           // staging buffer free again
         }
       } else {
         warp_arrive(&bars->bias_free[prev_buf]);
@@ -504,20 +431,19 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
     int item = 0;
     uint32_t acc2_phase = 0;          // acc2_full completes one phase per two-hidden-layer item only
     if (P.debug & 64) {               // development: layer-1 pipeline alone (no epilogue work, no layers 2/3)
-      for (; item < n_items; ++item) {
-        mbar_wait(&bars->acc1_full[item & 1], (uint32_t)((item >> 1) & 1));
-        warp_arrive(&bars->acc1_empty[item & 1]);
-      }
+      for (int tile = tile0; tile < P.n_tiles; tile += tile_step)
+        for (int t = t0; t < t1; ++t, ++item) {
+          mbar_wait(&bars->acc1_full[item & 1], (uint32_t)((item >> 1) & 1));
+          warp_arrive(&bars->acc1_empty[item & 1]);
+        }
     }
-    {
-      for (; item < n_items; ++item) {
-        const int it = item_begin + item;
-        const int t = it % W;
+    for (int tile = tile0; tile < ((P.debug & 64) ? 0 : P.n_tiles); tile += tile_step) {
+      for (int t = t0; t < t1; ++t, ++item) {
         const TrialDev& T = P.trial[t];
         const int buf = item & 1;
         const uint32_t par2 = (uint32_t)((item >> 1) & 1);
         const float* bias = reinterpret_cast<const float*>(smem + OFF_BIAS + buf * BIAS_BYTES);
-        if (W > 1 || item < 2) wait_prof<kProf>(&bars->bias_full[buf], par2, prof, PF_EPI_BIAS);
+        if (w > 1 || item < 2) wait_prof<kProf>(&bars->bias_full[buf], par2, prof, PF_EPI_BIAS);
         // ---- layer 1: acc1[buf] -> hidden (after layer 3 of the previous item has read the hidden tile)
         wait_prof<kProf>(&bars->acc1_full[buf], par2, prof, PF_EPI_ACC1);
         if (warp == 0) RFK_TRACE(3, 1);
@@ -552,7 +478,8 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
           if (warp == 0) RFK_TRACE(3, 4);
         }
         have_prev = true;
-        prev_it = it;
+        prev_tile = tile;
+        prev_t = t;
         prev_buf = buf;
       }
     }
@@ -583,8 +510,8 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
     int rstage = 0;
     uint32_t rphase = 0;
     int gs = 0;                                    // global step counter of this CTA
-    {
-      for (int item = 0; item < n_items; ++item) {
+    for (int tile = tile0; tile < P.n_tiles; tile += tile_step) {
+      for (int t = t0; t < t1; ++t) {
         for (int kb = 0; kb < n_kb; ++kb, ++gs) {
           mbar_wait(&bars->raw_full[rstage], rphase);
           // A stage gs % 2 was last read by the MMAs of step gs - 2
@@ -627,23 +554,25 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
   }
   if (warp == WARP_LOAD) {
     // =============================================================== loader: weights, raw query tiles, parameters
-    // Per step j: the W1 block of step j (cp.async.bulk of the pre-swizzled block into the B_STAGES-deep
-    // weight ring, as soon as the MMAs of step j - B_STAGES have completed) and the raw uint8 tile
-    // of step j (TMA tensor load into the RAW_STAGES-deep raw ring).  The second wait never blocks in
-    // steady state: the MMAs of step j - 4 completing implies the conversion of step j - 3 is done.
+    // Per step j, in the order the two slots come free: the raw uint8 tile of step j (TMA tensor load
+    // into the RAW_STAGES-deep raw ring, as soon as the conversion of step j - 3 has read its slot)
+    // and the W1 block of step j (cp.async.bulk of the pre-swizzled block into the B_STAGES-deep
+    // weight ring, as soon as the MMAs of step j - 4 have completed).
     // Per-item parameters (biases, W3: double buffered by item parity; W2: one buffer, released
     // as soon as the layer-2 MMAs of the previous item have completed) ride along as a third,
     // non-blocking cursor that is polled once per step; with a single trial nothing is reloaded.
-    const int total_items = (P.debug & 64) ? 0 : n_items;
+    int my_tiles = 0;
+    for (int tile = tile0; tile < P.n_tiles; tile += tile_step) ++my_tiles;
+    const int total_items = (P.debug & 64) ? 0 : my_tiles * w;
     const int n_atoms = (P.d + ATOM_K - 1) / ATOM_K;
-    int p_item = 0, p_t = item_begin % W, p_sub = 0, n2 = 0;
+    int p_item = 0, p_t = t0, p_sub = 0, n2 = 0;
     auto param_poll = [&](bool blocking) {
       // at most one action per call; returns when the cursor cannot advance (non-blocking mode)
       if (p_item >= total_items) return;
       const TrialDev& T = P.trial[p_t];
       const int buf = p_item & 1;
       const uint32_t par_free2 = (uint32_t)(((p_item >> 1) & 1) ^ 1);
-      if (p_sub < 2 && !(W > 1 || p_item < 2)) p_sub = 2;
+      if (p_sub < 2 && !(w > 1 || p_item < 2)) p_sub = 2;
       if (p_sub == 0) {
         if (blocking) mbar_wait(&bars->bias_free[buf], par_free2);
         else if (!mbar_test(&bars->bias_free[buf], par_free2)) return;
@@ -660,7 +589,7 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
         p_sub = 2;
         return;
       }
-      if (T.n_hidden == 2 && (W > 1 || n2 == 0)) {
+      if (T.n_hidden == 2 && (w > 1 || n2 == 0)) {
         if (blocking) mbar_wait(&bars->w2_free, (uint32_t)((n2 & 1) ^ 1));
         else if (!mbar_test(&bars->w2_free, (uint32_t)((n2 & 1) ^ 1))) return;
         const uint32_t w2_bytes = (uint32_t)((T.h1_pad + 63) / 64) * (uint32_t)T.h2_pad * 128u;
@@ -669,7 +598,7 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
       if (T.n_hidden == 2) ++n2;
       ++p_item;
       p_sub = 0;
-      if (++p_t == W) p_t = 0;
+      if (++p_t == t1) p_t = t0;
     };
     // Waiting for a ring slot must not starve the parameter cursor (the MMAs the slot waits for may
     // themselves be waiting, through the epilogue, for parameters): poll it between bounded waits.
@@ -688,20 +617,13 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
     for (int i = 0; i < 6; ++i) param_poll(false);
     int bstage = 0, rstage = 0;
     uint32_t bphase = 0, rphase = 0;
-    {
-      for (int it = item_begin; it < item_end; ++it) {
-        const int tile = it / W;
-        const TrialDev& T = P.trial[it - tile * W];
+    for (int tile = tile0; tile < P.n_tiles; tile += tile_step) {
+      for (int t = t0; t < t1; ++t) {
+        const TrialDev& T = P.trial[t];
         const uint32_t atom_bytes = (uint32_t)T.h1_pad * 128u;        // one 64-wide K atom of W1
         const uint8_t* src = T.w1;
         for (int kb = 0; kb < n_kb; ++kb) {
           const uint32_t bytes = atom_bytes * (uint32_t)(n_atoms - 2 * kb < 2 ? n_atoms - 2 * kb : 2);
-          wait_serving(&bars->step_done[bstage], bphase ^ 1u);
-          RFK_TRACE(1, 3);
-          if (P.debug & 1)
-            mbar_arrive_elect(&bars->b_full[bstage]);
-          else
-            bulk_g2s_expect_elect(smem + OFF_B + bstage * B_STAGE, src + (size_t)kb * 2 * atom_bytes, bytes, &bars->b_full[bstage]);
           wait_serving(&bars->raw_empty[rstage], rphase ^ 1u);
           RFK_TRACE(1, 1);
           if (P.debug & 32)
@@ -709,6 +631,12 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
           else
             tma_load_2d_expect_elect(smem + OFF_RAW + rstage * RAW_STAGE, &x_map, kb * KB, tile * TILE_M, RAW_STAGE,
                                      &bars->raw_full[rstage]);
+          wait_serving(&bars->step_done[bstage], bphase ^ 1u);
+          RFK_TRACE(1, 3);
+          if (P.debug & 1)
+            mbar_arrive_elect(&bars->b_full[bstage]);
+          else
+            bulk_g2s_expect_elect(smem + OFF_B + bstage * B_STAGE, src + (size_t)kb * 2 * atom_bytes, bytes, &bars->b_full[bstage]);
           if (++bstage == B_STAGES) { bstage = 0; bphase ^= 1u; }
           if (++rstage == RAW_STAGES) { rstage = 0; rphase ^= 1u; }
           param_poll(false);
@@ -730,11 +658,13 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
     // the turn so that the MMAs enter the pipe in step order.
     const int me = warp - WARP_MMA;
     const uint32_t b_lo0 = desc_lo_sw128(smem_base + OFF_B);
-    const int total_steps = n_items * n_kb;
-    int gs = 0;
-    {
-      for (int item = 0; item < n_items; ++item) {
-        const TrialDev& T = P.trial[(item_begin + item) % W];
+    int my_tiles = 0;
+    for (int tile = tile0; tile < P.n_tiles; tile += tile_step) ++my_tiles;
+    const int total_steps = my_tiles * w * n_kb;
+    int item = 0, gs = 0;
+    for (int tile = tile0; tile < P.n_tiles; tile += tile_step) {
+      for (int t = t0; t < t1; ++t, ++item) {
+        const TrialDev& T = P.trial[t];
         const int buf = item & 1;
         const uint32_t idesc1 = idesc_16bit_f32(kF16, TILE_M, T.h1_pad);
         const uint32_t d_tmem = tmem_base + COL_ACC1 + buf * HMAX;
@@ -796,13 +726,13 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
         mma4_f16_ts_elect(d_tmem, a, desc_from_lo(b), idesc, k0 != 0, ksteps - k0 < 4 ? ksteps - k0 : 4);
       }
     };
-    int n2 = 0;
-    {
-      for (int item = 0; item < ((P.debug & 64) ? 0 : n_items); ++item) {
-        const TrialDev& T = P.trial[(item_begin + item) % W];
+    int item = 0, n2 = 0;
+    for (int tile = tile0; tile < ((P.debug & 64) ? 0 : P.n_tiles); tile += tile_step) {
+      for (int t = t0; t < t1; ++t, ++item) {
+        const TrialDev& T = P.trial[t];
         const int buf = item & 1;
         if (T.n_hidden == 2) {
-          if (W > 1 || n2 == 0) wait_prof<kProf>(&bars->w2_full, (uint32_t)(n2 & 1), prof, PF_MMA_W23_FULL);
+          if (w > 1 || n2 == 0) wait_prof<kProf>(&bars->w2_full, (uint32_t)(n2 & 1), prof, PF_MMA_W23_FULL);
           ++n2;
           wait_prof<kProf>(&bars->hid_ready, hid_phase, prof, PF_MMA_HID_L2);
           RFK_TRACE(4, 1);
@@ -814,7 +744,7 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
           mma_commit_elect(&bars->w2_free);
           RFK_TRACE(4, 2);
         }
-        if (W > 1 || item < 2) wait_prof<kProf>(&bars->w3_full[buf], (uint32_t)((item >> 1) & 1), prof, PF_MMA_W23_FULL);
+        if (w > 1 || item < 2) wait_prof<kProf>(&bars->w3_full[buf], (uint32_t)((item >> 1) & 1), prof, PF_MMA_W23_FULL);
         wait_prof<kProf>(&bars->hid_ready, hid_phase, prof, PF_MMA_HID_L3);
         RFK_TRACE(4, 3);
         hid_phase ^= 1u;
@@ -929,29 +859,10 @@ void fused_release(rfk_mlp* h) {
   h->fused = nullptr;
 }
 
-namespace {
-// balanced schedule: flags [grid][w] (rounded up to 256 bytes), then scratch [grid][w][128][C] floats
-inline size_t balanced_flag_bytes(int grid, int w) { return ((size_t)grid * w * sizeof(unsigned) + 255) / 256 * 256; }
-inline size_t balanced_bytes(int grid, int w, int n_classes) {
-  return balanced_flag_bytes(grid, w) + (size_t)grid * w * TILE_M * n_classes * sizeof(float);
-}
-inline bool split_applies(int w, int64_t n_tiles) { return w > 1 && n_tiles * w <= (int64_t)num_sms(); }
-inline bool balanced_applies(int w, int64_t n_tiles) {
-  // Measured on B200: worth it only when whole tiles would leave more than half of the SMs without
-  // work (W 8, n 8192: 46.5 -> 42.4 us).  With a tile or more per SM the idle SMs of the last wave
-  // hand their power budget to the busy ones (the chip runs at its power cap), and the scratch round
-  // trip of the straddling tiles costs more than the better balance gains (W 8, n 65536: 154 -> 160 us).
-  if (w <= 1 || split_applies(w, n_tiles)) return false;
-  if (getenv("RFK_FORCE_BALANCE") != nullptr) return true;     // tests: exercise straddling tiles at any size
-  return 2 * n_tiles <= (int64_t)num_sms();
-}
-}  // namespace
-
 size_t fused_workspace_bytes(int w, int n_classes, int64_t n) {
-  // optional scratch: without it the kernel falls back to whole tiles per CTA
+  // split mode (see the kernel): used when all (tile, trial) items fit on the GPU at once
   const int64_t n_tiles = (n + TILE_M - 1) / TILE_M;
-  if (split_applies(w, n_tiles)) return (size_t)w * (size_t)n * n_classes * sizeof(float);
-  if (balanced_applies(w, n_tiles)) return balanced_bytes(num_sms(), w, n_classes);
+  if (w > 1 && n_tiles * w <= (int64_t)num_sms()) return (size_t)w * (size_t)n * n_classes * sizeof(float);
   return 0;
 }
 
@@ -986,32 +897,12 @@ int fused_forward(rfk_mlp* const* trials, int w, int total_trials, const uint8_t
   }
   const int sms = num_sms();
   int grid = P.n_tiles < sms ? P.n_tiles : sms;
-  const bool split = split_applies(w, P.n_tiles) && ws != nullptr &&
-                     ws_bytes >= (size_t)w * (size_t)n * P.n_classes * sizeof(float) && getenv("RFK_NO_SPLIT") == nullptr;
+  const size_t split_bytes = fused_workspace_bytes(w, P.n_classes, n);
+  const bool split = split_bytes != 0 && ws != nullptr && ws_bytes >= split_bytes && getenv("RFK_NO_SPLIT") == nullptr;
   if (split) {
     P.split = 1;
     P.out = static_cast<float*>(ws);
     grid = P.n_tiles * w;
-  } else if (balanced_applies(w, P.n_tiles) && ws != nullptr && ws_bytes >= balanced_bytes(sms, w, P.n_classes) &&
-             (reinterpret_cast<uintptr_t>(ws) & 15) == 0 && getenv("RFK_NO_BALANCE") == nullptr) {
-    // Contribution flags carry a launch number, so they never need resetting; a workspace this
-    // device has not seen in the previous call may hold anything, so its flags are cleared once.
-    static std::atomic<unsigned> launch_counter{0};
-    static void* last_ws[64] = {nullptr};
-    static int last_w[64] = {0};
-    unsigned epoch = launch_counter.fetch_add(1) + 1;
-    if (epoch == 0) epoch = launch_counter.fetch_add(1) + 1;
-    grid = (long long)P.n_tiles * w < sms ? P.n_tiles * w : sms;
-    P.balanced = 1;
-    P.epoch = epoch;
-    P.flags = static_cast<unsigned*>(ws);
-    P.scratch = reinterpret_cast<float*>(static_cast<char*>(ws) + balanced_flag_bytes(sms, w));
-    const int dev = trials[0]->device & 63;
-    if (last_ws[dev] != ws || last_w[dev] != w) {          // new buffer or new layout: stale bytes where the flags go
-      RFK_CUDA_TRY(cudaMemsetAsync(ws, 0, balanced_flag_bytes(sms, w), st));
-      last_ws[dev] = ws;
-      last_w[dev] = w;
-    }
   }
   const char* prof_env = getenv("RFK_FUSED_PROF");
   if (prof_env != nullptr && atoi(prof_env) != 0 && trials[0]->dtype == RFK_F16) {

@@ -240,32 +240,6 @@ def test_ensemble_forward(compute, tol, w, n):
         t.close()
 
 
-@pytest.mark.parametrize('w,n', [(8, 8192 + 37), (3, 20000), (5, 33000), (2, 19000), (8, 65536)])
-def test_balanced_schedule_matches_whole_tile_schedule(w, n, monkeypatch):
-    """Batches whose tiles do not divide over the SMs: CTAs take equal ranges of (tile, trial) items and a
-    tile may straddle CTAs (contributions through scratch).  Same bits as whole tiles per CTA and as
-    "each trial alone, then kernel 3"."""
-    dead = synth.dead_mask(784)
-    shapes = [(2, 128), (1, 36), (2, 7), (2, 128), (1, 128), (2, 64), (1, 2), (2, 100)]
-    params = [synth.make_trial(t, 28, 1, *shapes[t], dead=dead) for t in range(w)]
-    x = torch.from_numpy(synth.make_queries(n, 28, 1, 'uniform', seed=5, dead=dead)).cuda()
-    trials = [engine.Trial(p) for p in params]
-    monkeypatch.setenv('RFK_FORCE_BALANCE', '1')     # the library picks this schedule only for few tiles per SM
-    ens = engine.Ensemble(trials)
-    assert ens.workspace_bytes(n) > 0
-    got = ens.forward(x)
-    again = ens.forward(x)                      # flags of the first launch must not satisfy the second
-    assert torch.equal(got, again)
-    monkeypatch.setenv('RFK_NO_BALANCE', '1')
-    whole = ens.forward(x)
-    monkeypatch.delenv('RFK_NO_BALANCE')
-    monkeypatch.delenv('RFK_FORCE_BALANCE')
-    assert torch.equal(got, whole)
-    assert torch.equal(got, engine.ensemble_mean([t.forward(x) for t in trials]))
-    for t in trials:
-        t.close()
-
-
 def test_full_size_properties_batch_65536():
     """BASELINE config 3 size: size-independent properties instead of an oracle pass."""
     dead = synth.dead_mask(784)
