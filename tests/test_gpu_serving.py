@@ -48,6 +48,22 @@ def test_dropin_model_file_through_the_plugin_harness(S, tmp_path, monkeypatch, 
     model.destroy()
 
 
+def test_dropin_loads_a_reference_made_h5_parameter_dict(tmp_path, monkeypatch):
+    """What a reference train worker stored: {'h5_model_base64': model.save() bytes} (TfFeedForward.py:102-118)."""
+    import base64
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    import h5_writer
+    monkeypatch.chdir(tmp_path)
+    p = synth.make_trial(5, 28, 1, 2, 64, data_kind='fashion')
+    wire = {'h5_model_base64': base64.b64encode(h5_writer.keras_model_file(p, 28)).decode('utf-8')}
+    queries = synth.make_queries(50, 28, 1, 'fashion', seed=4).tolist()
+    model, preds = serve_model_class(MODEL_FILE, 'TfFeedForward', TaskType.IMAGE_CLASSIFICATION, wire, queries, _knobs(p))
+    assert np.abs(np.asarray(preds) - np.asarray(ff.serve_batch([p], queries))).max() <= 2e-3
+    assert np.array_equal(model.dump_parameters()['kernels'][1], p['kernels'][1])
+    model.destroy()
+
+
 def test_fp32_mode_of_the_dropin(tmp_path, monkeypatch):
     monkeypatch.chdir(tmp_path)
     monkeypatch.setenv('RAFIKI_B200_COMPUTE', 'f32')
