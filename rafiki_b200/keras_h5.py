@@ -142,6 +142,7 @@ class H5File:
                 if mtype == MSG_CONTINUATION:
                     b = _Cursor(body)
                     blocks.append((self.base + b.u(self.O), b.u(self.L)))
+                    _need(len(out) <= 65536, 'object header with an endless chain of continuation blocks')
         return out
 
     def _messages_v2(self, c):
@@ -153,9 +154,11 @@ class H5File:
         if hflags & 0x10:
             c.skip(4)                       # attribute phase-change thresholds
         size = c.u(1 << (hflags & 3))
-        out, blocks = [], [(c.pos, size)]
+        out, blocks, seen = [], [(c.pos, size)], set()
         while blocks:
             pos, size = blocks.pop(0)
+            _need(pos not in seen, 'object header continuation blocks form a cycle')
+            seen.add(pos)
             c = _Cursor(self.buf, pos)
             end = pos + size
             while c.pos + 4 <= end:
@@ -206,11 +209,12 @@ class H5File:
         data = c.u(self.O)
         return self.buf[self.base + data:self.base + data + size]
 
-    def _walk_group_btree(self, addr, heap, out):
+    def _walk_group_btree(self, addr, heap, out, below=256):
         c = self.at(addr)
         _need(c.take(4) == b'TREE', 'B-tree signature missing at %d' % addr)
         node_type, level, used = c.u(1), c.u(1), c.u(2)
         _need(node_type == 0, 'B-tree node type %d where a group node is expected' % node_type)
+        _need(level < below, 'B-tree levels do not decrease towards the leaves')
         c.skip(2 * self.O)                  # siblings
         children = []
         for _ in range(used):
@@ -218,7 +222,7 @@ class H5File:
             children.append(c.u(self.O))
         for child in children:
             if level > 0:
-                self._walk_group_btree(child, heap, out)
+                self._walk_group_btree(child, heap, out, level)
                 continue
             s = self.at(child)
             _need(s.take(4) == b'SNOD', 'symbol table node signature missing at %d' % child)
@@ -226,7 +230,8 @@ class H5File:
             for _ in range(s.u(2)):
                 name_off, obj = s.u(self.O), s.u(self.O)
                 s.skip(24)                  # cache type, reserved, scratch pad
-                end = heap.index(b'\0', name_off)
+                end = heap.find(b'\0', name_off)
+                _need(0 <= name_off < len(heap) and end >= 0, 'link name outside the local heap')
                 out[heap[name_off:end].decode('utf-8')] = obj
 
     def _link_message(self, body):
@@ -243,7 +248,9 @@ class H5File:
 
     def resolve(self, path, start=None):
         addr = self.root_addr if start is None else start
-        for part in [p for p in path.split('/') if p]:
+        parts = [p for p in path.split('/') if p]
+        _need(len(parts) <= 64, 'path too deep')
+        for part in parts:
             table = self.links(addr)
             _need(part in table, 'no object named %r (have %s)' % (part, sorted(table)))
             addr = table[part]

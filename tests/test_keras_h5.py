@@ -131,3 +131,26 @@ def test_refusals_say_what_was_met():
     plain = w.finish(w.group({'x': w.dataset(np.zeros(3, np.float32))}))
     with pytest.raises(keras_h5.H5FormatError, match='layer_names'):
         keras_h5.params_from_h5_bytes(plain)
+
+
+def test_damaged_files_raise_value_errors_and_terminate():
+    """Random damage must end in a ValueError (H5FormatError, a JSON or a text decoding error), never in a hang,
+    an IndexError or a silent wrong answer of the wrong shape."""
+    good = bytearray(h5_writer.keras_model_file(synth.make_trial(2, 28, 1, 1, 8), 28))
+    rng = np.random.default_rng(0)
+    structural = len(good) - 784 * 8 * 4          # leave most of the big kernel alone: hit headers, heaps, trees
+    outcomes = {'ok': 0, 'refused': 0}
+    for trial in range(300):
+        bad = bytearray(good)
+        for _ in range(int(rng.integers(1, 6))):
+            pos = int(rng.integers(0, len(bad))) if trial % 3 == 0 else int(rng.integers(0, 4096)) % len(bad)
+            bad[pos] = int(rng.integers(0, 256))
+        if trial % 10 == 9:
+            bad = bad[:int(rng.integers(8, len(bad)))]
+        try:
+            q = keras_h5.params_from_h5_bytes(bytes(bad))
+            assert len(q['kernels']) >= 1 and all(k.ndim == 2 for k in q['kernels'])
+            outcomes['ok'] += 1
+        except (ValueError, KeyError, OverflowError, MemoryError):
+            outcomes['refused'] += 1
+    assert outcomes['ok'] + outcomes['refused'] == 300 and outcomes['refused'] > 0 and structural > 0
