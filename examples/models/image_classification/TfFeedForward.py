@@ -4,10 +4,13 @@ examples/models/image_classification/TfFeedForward.py, served by hand-written sm
 Same class name, knob configuration (``:20-28``) and ``BaseModel`` methods.  What changed is
 underneath:
 
-* ``predict`` (``:89-97``): the queries are resized exactly as ``dataset_utils.resize_as_images``
-  does, uploaded as uint8 and pushed through ``librafiki_b200`` (decode + BatchNormalization +
+* ``predict`` (``:89-97``): the queries are uploaded as uint8 at the size they arrive in, resized
+  on the GPU exactly as ``dataset_utils.resize_as_images`` does (Pillow NEAREST,
+  ``rfk_resize_decode_u8``) and pushed through ``librafiki_b200`` (decode + BatchNormalization +
   Dense/ReLU layers + softmax on tcgen05 tensor cores with fp16 operands, or true fp32 with
-  ``RAFIKI_B200_COMPUTE=f32``, or bf16 operands with ``=bf16``); the result is ``probs.tolist()`` as before.
+  ``RAFIKI_B200_COMPUTE=f32``, or bf16 operands with ``=bf16``); the result is ``probs.tolist()`` as
+  before.  Besides nested lists, ``predict`` takes a ``uint8`` ndarray ``[n, S, S(, ch)]`` (no
+  per-pixel Python conversion); ``predict_array`` also returns an ndarray.
 * ``dump_parameters`` / ``load_parameters`` (``:102-135``): the dict holds the Keras tensors as
   raw arrays (Dense kernels ``[in, out]``, biases, BatchNormalization gamma / beta / moving mean /
   moving variance) instead of a base64 HDF5 file, because neither TensorFlow nor h5py exists on
@@ -56,8 +59,11 @@ class TfFeedForward(BaseModel):
     def predict(self, queries):
         if len(queries) == 0:
             return []
-        probs = self.predict_tensor(self._queries_to_device(queries))
-        return probs.cpu().numpy().tolist()
+        return self.predict_array(queries).tolist()
+
+    def predict_array(self, queries):
+        """Binary fast path: list or ``uint8`` ndarray ``[n, S, S(, ch)]`` -> ``float32`` ndarray ``[n, C]``."""
+        return self.predict_tensor(self._queries_to_device(queries)).cpu().numpy()
 
     def predict_tensor(self, x):
         """Tensor fast path: ``uint8 [n, S, S(, ch)]`` CUDA tensor -> ``float32 [n, C]`` CUDA tensor."""
@@ -66,10 +72,19 @@ class TfFeedForward(BaseModel):
         return self._trial.forward(x)
 
     def _queries_to_device(self, queries):
+        """uint8 frames at their own size -> device -> Pillow-NEAREST resize ON THE GPU to the
+        trial's ``image_size`` (rafiki/model/dataset.py:76-78; the default knob is 32 for 28x28 queries)."""
         import torch
+        from rafiki_b200 import engine
+        from rafiki_b200.model.dataset import queries_to_uint8
         im_sz = self._image_size()
-        X = dataset_utils.resize_as_images(queries, image_size=[im_sz, im_sz])
-        return torch.from_numpy(X).cuda()
+        frames = np.ascontiguousarray(queries_to_uint8(queries))
+        x = torch.from_numpy(frames).cuda()
+        if frames.ndim >= 3 and (frames.shape[1] != im_sz or frames.shape[2] != im_sz):
+            if frames.shape[1] != frames.shape[2]:
+                raise ValueError('queries must be square images, got {}'.format(frames.shape[1:]))
+            x = engine.resize_decode_u8(x, im_sz)
+        return x
 
     def _image_size(self):
         im_sz = self._knobs.get('image_size')

@@ -1,5 +1,8 @@
 // Error reporting, version and device checks of librafiki_b200.
 #include <stdarg.h>
+#include <string.h>
+
+#include <atomic>
 
 #include "rfk_common.cuh"
 
@@ -12,6 +15,29 @@ void set_error(const char* fmt, ...) {
   va_start(ap, fmt);
   vsnprintf(g_err, sizeof(g_err), fmt, ap);
   va_end(ap);
+}
+
+// Launch accounting: one counter per kernel name (the string literals passed to RFK_LAUNCH_CHECK).
+// A slot is claimed with a compare-exchange on its name pointer; counting is one relaxed add.
+namespace {
+constexpr int kMaxKernelNames = 64;
+std::atomic<const char*> g_kernel_name[kMaxKernelNames];
+std::atomic<unsigned long long> g_kernel_launches[kMaxKernelNames];
+}  // namespace
+
+void count_launch(const char* name) {
+  for (int i = 0; i < kMaxKernelNames; ++i) {
+    const char* cur = g_kernel_name[i].load(std::memory_order_acquire);
+    if (cur == nullptr) {
+      const char* expected = nullptr;
+      if (g_kernel_name[i].compare_exchange_strong(expected, name, std::memory_order_acq_rel)) cur = name;
+      else cur = expected;
+    }
+    if (cur == name || strcmp(cur, name) == 0) {
+      g_kernel_launches[i].fetch_add(1, std::memory_order_relaxed);
+      return;
+    }
+  }
 }
 
 int num_sms() {
@@ -32,6 +58,17 @@ int num_sms() {
 extern "C" int rfk_version(void) { return RFK_VERSION; }
 
 extern "C" const char* rfk_last_error(void) { return rfk::g_err; }
+
+extern "C" unsigned long long rfk_launch_count(const char* name_part) {
+  unsigned long long total = 0;
+  for (int i = 0; i < rfk::kMaxKernelNames; ++i) {
+    const char* nm = rfk::g_kernel_name[i].load(std::memory_order_acquire);
+    if (nm == nullptr) break;
+    if (name_part == nullptr || name_part[0] == 0 || strstr(nm, name_part) != nullptr)
+      total += rfk::g_kernel_launches[i].load(std::memory_order_relaxed);
+  }
+  return total;
+}
 
 extern "C" int rfk_device_check(int device) {
   int count = 0;

@@ -29,15 +29,22 @@
 //                          weight block into a 4-deep ring and one TMA tensor load of the 128 x 128-byte
 //                          uint8 tile (out-of-range rows / columns arrive as zeros) into a 3-deep
 //                          raw ring; W2, W3 and the biases of the next items as a third cursor
-//   warps 17-18 MMA issuers, layer 1: alternate K steps (while one issues its eight MMAs the other
-//                          commits and waits for its operands); A from tensor memory, B from shared
-//                          memory; accumulators in TMEM (2 x 128 columns, double buffered so the
-//                          epilogue of one item overlaps the MMAs of the next)
+//   warp 17     MMA issuer, layer 1: A from tensor memory, B from shared memory; accumulators in
+//                          TMEM (2 x 128 columns, double buffered so the epilogue of one item
+//                          overlaps the MMAs of the next).  ONE thread issues every MMA of an
+//                          accumulator: tcgen05.mma instructions of one thread execute in issue
+//                          order, those of two threads do not (measured: two warps taking alternate
+//                          K steps behind a named-barrier token gave results that differed in the last
+//                          bits from launch to launch, because fp32 accumulation is not associative).
+//   warp 18     spare (keeps warpgroup 4 complete for setmaxnreg)
 //   warp 19     MMA issuer for layers 2 and 3 (hidden tile x W2 / W3); layer 2 accumulates into the
 //                          layer-1 buffer its epilogue has just drained, layer 3 into 16 columns
 // Every tcgen05.mma / TMA / bulk-copy issue is warp-convergent with an elect.sync predicate on the
-// instruction itself: from inside an `if (lane == 0)` region each of them costs a few hundred
-// cycles (the compiler wraps instructions with uniform-register operands in a serialising loop).
+// instruction itself, and the warp index is taken through a shuffle so that the compiler knows it is
+// warp-uniform: addresses, descriptors and loop counters of the issuing roles then live in uniform
+// registers and each MMA / bulk copy is one instruction.  (With `threadIdx.x >> 5` every operand
+// went through R2UR moves, ~60 cycles per MMA; from inside an `if (lane == 0)` region each issue
+// costs a few hundred cycles.)
 // A work item is (tile of 128 queries, trial); items of one tile run back to back so the tile
 // stays hot in L2 and the ensemble sum never leaves registers.
 //
@@ -90,13 +97,13 @@ static_assert(OFF_W2 % 1024 == 0 && OFF_W3 % 1024 == 0 && OFF_B % 1024 == 0 && O
 static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
 
 // Five warpgroups (setmaxnreg works per warpgroup): 0-1 epilogue, 2-3 converters, 4 = loader, MMA
-// issuer for layer 1, parameter loader, MMA issuer for layers 2/3.  The kernel starts with 96 registers per thread;
+// issuer for layer 1, a spare warp, MMA issuer for layers 2/3.  The kernel starts with 96 registers per thread;
 // the light roles give registers back and the epilogue warps take them.
 constexpr int kEpiWarps = 8, kConvWarps = 8;
 constexpr int kEpiThreads = kEpiWarps * 32;                   // 256
 constexpr int kConvThreads = kConvWarps * 32;                 // 256: half a row (64 bytes) per thread per step
 constexpr int kThreads = (kEpiWarps + kConvWarps + 4) * 32;   // 640
-constexpr int WARP_LOAD = kEpiWarps + kConvWarps, WARP_MMA = WARP_LOAD + 1 /* and + 2 */, WARP_TAIL = WARP_LOAD + 3;
+constexpr int WARP_LOAD = kEpiWarps + kConvWarps, WARP_MMA = WARP_LOAD + 1, WARP_TAIL = WARP_LOAD + 3;
 constexpr int kRegsEpi = 136, kRegsLight = 56;
 
 constexpr int TMEM_COLS = 512;
@@ -287,7 +294,7 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
   uint8_t* smem = smem_raw;
   Bars* bars = reinterpret_cast<Bars*>(smem + OFF_BAR);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + OFF_TMEM_SLOT);
-  const int warp = threadIdx.x >> 5;
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);   // provably warp-uniform for the compiler
   const int lane = threadIdx.x & 31;
   if ((smem_u32(smem) & 1023u) != 0u) {        // the swizzled operand tiles need 1024-byte alignment
     if (threadIdx.x == 0) printf("rafiki_b200: dynamic shared memory is not 1024-byte aligned\n");
@@ -305,7 +312,7 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
       mbar_init(&bars->raw_empty[s], kConvWarps);
     }
     for (int b = 0; b < 2; ++b) {
-      mbar_init(&bars->acc1_full[b], 2);                 // one commit from each layer-1 issuer
+      mbar_init(&bars->acc1_full[b], 1);
       mbar_init(&bars->acc1_empty[b], kEpiWarps);
       mbar_init(&bars->bias_full[b], 1);
       mbar_init(&bars->bias_free[b], kEpiWarps);
@@ -549,7 +556,7 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
       }
     }
   } else {
-    // warpgroup 4: loader, two MMA issuers, parameter loader -- all give registers back
+    // warpgroup 4: loader, layer-1 MMA issuer, spare, layers-2/3 MMA issuer -- all give registers back
     asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsLight));
   }
   if (warp == WARP_LOAD) {
@@ -644,23 +651,14 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
       }
     }
     while (p_item < total_items) param_poll(true);
-  } else if (warp == WARP_MMA || warp == WARP_MMA + 1) {
-    // =============================================================== MMA issuers, layer 1 (two warps)
+  } else if (warp == WARP_MMA) {
+    // =============================================================== MMA issuer, layer 1
     // Executed by all 32 lanes in lock step (mbarrier waits included); the *_elect helpers pick
     // one lane per statement, so there is no divergent region.  A comes from tensor memory (the
     // converters' ring, 8 columns per 16-element K step), B from shared memory: the descriptor is a
     // constant upper word plus (address >> 4) in the lower word.  One commit per step releases both
     // the weight stage (to the loader) and the A stage (to the converters).
-    // Issuing eight MMAs costs about as many cycles as executing them (operands travel through
-    // uniform registers), so one warp alone leaves the tensor pipe idle while it commits and polls
-    // the next step's barriers.  Two warps take alternate steps: while one issues, the other commits
-    // its previous step and waits for its next operands; a named-barrier token (ids 2 and 3) passes
-    // the turn so that the MMAs enter the pipe in step order.
-    const int me = warp - WARP_MMA;
     const uint32_t b_lo0 = desc_lo_sw128(smem_base + OFF_B);
-    int my_tiles = 0;
-    for (int tile = tile0; tile < P.n_tiles; tile += tile_step) ++my_tiles;
-    const int total_steps = my_tiles * w * n_kb;
     int item = 0, gs = 0;
     for (int tile = tile0; tile < P.n_tiles; tile += tile_step) {
       for (int t = t0; t < t1; ++t, ++item) {
@@ -668,23 +666,12 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
         const int buf = item & 1;
         const uint32_t idesc1 = idesc_16bit_f32(kF16, TILE_M, T.h1_pad);
         const uint32_t d_tmem = tmem_base + COL_ACC1 + buf * HMAX;
-        bool acc_ready = false;
+        wait_prof<kProf>(&bars->acc1_empty[buf], (uint32_t)(((item >> 1) & 1) ^ 1), prof, PF_MMA_ACC1_EMPTY);
         for (int kb = 0; kb < n_kb; ++kb, ++gs) {
-          if ((gs & 1) != me) continue;
-          if (!acc_ready) {
-            wait_prof<kProf>(&bars->acc1_empty[buf], (uint32_t)(((item >> 1) & 1) ^ 1), prof, PF_MMA_ACC1_EMPTY);
-            acc_ready = true;
-          }
           const int as = gs % A_STAGES, bs = gs % B_STAGES;
           wait_prof<kProf>(&bars->b_full[bs], (uint32_t)((gs / B_STAGES) & 1), prof, PF_MMA_W23_FULL);
           wait_prof<kProf>(&bars->a_full[as], (uint32_t)((gs / A_STAGES) & 1), prof, PF_MMA_FULL);
-          if (gs > 0) {                     // my turn: the other warp has issued step gs - 1
-            if (me == 0)
-              asm volatile("bar.sync 2, 64;" ::: "memory");
-            else
-              asm volatile("bar.sync 3, 64;" ::: "memory");
-          }
-          if (me == 0) RFK_TRACE(2, 1);
+          RFK_TRACE(2, 1);
           tc_fence_after_sync();
           if (!(P.debug & 4)) {
             // two 64-wide atoms per step; the ragged end of the row may leave the second one short or empty
@@ -696,18 +683,10 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
               mma4_f16_ts_elect(d_tmem, a + 32u, desc_from_lo(b + (((uint32_t)T.h1_pad * 128u) >> 4)), idesc1, 1u,
                                 k16 - 4 < 4 ? k16 - 4 : 4);
           }
-          if (me == 0) RFK_TRACE(2, 2);
-          tc_fence_before_sync();
-          if (gs + 1 < total_steps) {       // pass the turn
-            if (me == 0)
-              asm volatile("bar.arrive 3, 64;" ::: "memory");
-            else
-              asm volatile("bar.arrive 2, 64;" ::: "memory");
-          }
+          RFK_TRACE(2, 2);
           mma_commit_elect(&bars->step_done[bs]);
-          if (me == 0) RFK_TRACE(2, 3);
+          RFK_TRACE(2, 3);
         }
-        // completes once the MMAs this warp issued for the item are done (at once if it had no step)
         mma_commit_elect(&bars->acc1_full[buf]);
       }
     }

@@ -15,6 +15,7 @@ namespace rfk {
 
 void set_error(const char* fmt, ...);
 int num_sms();  // SM count of the current device (cached per device)
+void count_launch(const char* kernel_name);  // launch accounting behind rfk_launch_count()
 
 #define RFK_CUDA_TRY(expr)                                                                   \
   do {                                                                                       \
@@ -33,6 +34,7 @@ int num_sms();  // SM count of the current device (cached per device)
       rfk::set_error("launch of %s failed: %s", name, cudaGetErrorString(_e));               \
       return RFK_ERR_CUDA;                                                                   \
     }                                                                                        \
+    rfk::count_launch(name);                                                                 \
   } while (0)
 
 #define RFK_REQUIRE(cond, ...)                                                               \

@@ -47,19 +47,35 @@ def _check_queries(x, d):
     return n
 
 
-class _Workspace:
-    """Grow-only device scratch owned by an engine object."""
+class Workspace:
+    """Grow-only device scratch for the calls of ONE stream.
 
-    def __init__(self, device):
+    The kernels of a call write their intermediates here (per-trial probabilities of the small-batch
+    schedule, activations of the layered paths) and a later kernel of the same call reads them, so
+    two calls that may overlap on the GPU (different streams) must not share one: every
+    :class:`HostPipeline` slot owns its own, and ``forward(..., workspace=...)`` takes one
+    explicitly.  Growing never frees the old block -- kernels already enqueued may still use it --
+    it is kept until the object dies.
+    """
+
+    def __init__(self, device, nbytes=0):
         self.device = device
         self.buf = None
+        self._retired = []
+        if nbytes:
+            self.get(nbytes)
 
     def get(self, nbytes):
         if nbytes == 0:
             return ctypes.c_void_p(0), 0
         if self.buf is None or self.buf.numel() < nbytes:
+            if self.buf is not None:
+                self._retired.append(self.buf)
             self.buf = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
         return ctypes.c_void_p(self.buf.data_ptr()), self.buf.numel()
+
+
+_Workspace = Workspace
 
 
 class Trial:
@@ -77,21 +93,28 @@ class Trial:
         self.d = info['d']
         self.n_classes = info['n_classes']
         self.fused = info['fused']
-        self._ws = _Workspace(self.device)
+        # geometry of the images the trial was trained on (S x S x ch, flattened to d features)
+        self.image_size = int(params['image_size']) if params.get('image_size') else None
+        if self.image_size is None or self.d % (self.image_size ** 2):
+            self.image_size = next((s for ch in (1, 3) for s in [int(round((self.d / ch) ** 0.5))]
+                                    if s * s * ch == self.d), None)
+        self.channels = self.d // (self.image_size ** 2) if self.image_size else 1
+        self._ws = Workspace(self.device)
 
     def workspace_bytes(self, n):
         out = ctypes.c_size_t()
         _native.check(self._lib.rfk_mlp_workspace_bytes(self.handle, n, ctypes.byref(out)))
         return out.value
 
-    def forward(self, x, out=None, stream=None):
-        """``uint8 [n, ...]`` CUDA tensor -> ``float32 [n, C]`` class probabilities."""
+    def forward(self, x, out=None, stream=None, workspace=None):
+        """``uint8 [n, ...]`` CUDA tensor -> ``float32 [n, C]`` class probabilities.  ``workspace``:
+        a :class:`Workspace` of the calling stream (default: the trial's own, for one stream)."""
         if self.handle is None:
             raise RuntimeError('trial was destroyed')
         n = _check_queries(x, self.d)
         if out is None:
             out = torch.empty((n, self.n_classes), dtype=torch.float32, device=self.device)
-        ws, ws_bytes = self._ws.get(self.workspace_bytes(n))
+        ws, ws_bytes = (workspace or self._ws).get(self.workspace_bytes(n))
         with torch.cuda.device(self.device):
             _native.check(self._lib.rfk_mlp_forward(self.handle, x.data_ptr(), n, out.data_ptr(), ws, ws_bytes,
                                                     _stream_ptr(stream)))
@@ -122,23 +145,27 @@ class Ensemble:
         self.n_classes = trials[0].n_classes
         self.total_trials = len(trials) if total_trials is None else int(total_trials)
         self._handles = _native.handle_array([t.handle for t in self.trials])
-        self._ws = _Workspace(self.device)
+        self._ws = Workspace(self.device)
         self._ws_bytes = {}
         self.fused = all(t.fused for t in self.trials)
+        self.image_size = trials[0].image_size
+        self.channels = trials[0].channels
 
     def workspace_bytes(self, n):
         out = ctypes.c_size_t()
         _native.check(self._lib.rfk_ensemble_workspace_bytes(self._handles, len(self.trials), n, ctypes.byref(out)))
         return out.value
 
-    def forward(self, x, out=None, stream=None):
+    def forward(self, x, out=None, stream=None, workspace=None):
+        """``workspace``: a :class:`Workspace` of the calling stream (default: the ensemble's own,
+        which serves one stream -- calls on several streams each bring theirs)."""
         n = _check_queries(x, self.d)
         if out is None:
             out = torch.empty((n, self.n_classes), dtype=torch.float32, device=self.device)
         need = self._ws_bytes.get(n)
         if need is None:
             need = self._ws_bytes[n] = self.workspace_bytes(n)
-        ws, ws_bytes = self._ws.get(need)
+        ws, ws_bytes = (workspace or self._ws).get(need)
         if torch.cuda.current_device() == self.device.index:      # the common case: no device switch
             _native.check(self._lib.rfk_ensemble_forward(self._handles, len(self.trials), self.total_trials,
                                                          x.data_ptr(), n, out.data_ptr(), ws, ws_bytes,
@@ -182,13 +209,18 @@ def decode_u8(x, scale=None, shift=None, out_dtype=torch.bfloat16, ld_out=None, 
     return out
 
 
-def resize_decode_u8(x, s_out, scale=None, shift=None, out_dtype=torch.uint8, stream=None):
+def resize_decode_u8(x, s_out, scale=None, shift=None, out_dtype=torch.uint8, stream=None, out=None):
     """Pillow-NEAREST resize (+ optional decode): ``uint8 [n, s, s(, ch)]`` -> ``[n, s_out*s_out*ch]``."""
     lib = _native.load()
     n, s_in = x.shape[0], x.shape[1]
     ch = x.shape[3] if x.dim() == 4 else 1
     d = s_out * s_out * ch
-    out = torch.empty((n, d), dtype=out_dtype, device=x.device)
+    if out is None:
+        out = torch.empty((n, d), dtype=out_dtype, device=x.device)
+    else:
+        out_dtype = out.dtype
+        if tuple(out.shape) != (n, d) or not out.is_contiguous():
+            raise ValueError('out must be a contiguous [{}, {}] tensor'.format(n, d))
     code = {torch.uint8: -1, torch.float32: _native.RFK_F32, torch.bfloat16: _native.RFK_BF16}[out_dtype]
     sp = ctypes.c_void_p(scale.data_ptr()) if scale is not None else ctypes.c_void_p(0)
     hp = ctypes.c_void_p(shift.data_ptr()) if shift is not None else ctypes.c_void_p(0)
@@ -198,30 +230,73 @@ def resize_decode_u8(x, s_out, scale=None, shift=None, out_dtype=torch.uint8, st
     return out
 
 
-class HostPipeline:
-    """Pinned-host hand-off around an :class:`Ensemble` (or :class:`Trial`).
+def frames_as_uint8(batch, frame_shape=None):
+    """Binary ingress: ``uint8`` frames without a per-pixel Python conversion.
 
-    ``serve(batch_u8_numpy) -> float32 numpy [n, C]`` copies the batch from pinned host memory
-    to the device, runs the engine, and copies the probabilities back, all on one stream; with
-    ``depth`` > 1 slots, ``submit``/``collect`` keep several batches in flight so the copies of
-    one batch overlap the kernels of another.
+    ``batch`` is an ``ndarray`` of dtype uint8 shaped ``[n, S, S(, ch)]`` (or ``[n, d]``), or a
+    bytes-like object holding ``n`` frames back to back (``frame_shape`` gives one frame's shape).
+    Returns a C-contiguous ``uint8 [n, ...]`` array that shares the caller's memory when it can.
+    """
+    if isinstance(batch, (bytes, bytearray, memoryview)):
+        if frame_shape is None:
+            raise ValueError('a bytes batch needs frame_shape')
+        per = int(np.prod(frame_shape))
+        a = np.frombuffer(batch, dtype=np.uint8)
+        if per == 0 or a.size % per:
+            raise ValueError('{} bytes are not a whole number of {}-byte frames'.format(a.size, per))
+        return a.reshape((a.size // per,) + tuple(int(v) for v in frame_shape))
+    a = np.asarray(batch)
+    if a.dtype != np.uint8:
+        raise TypeError('binary batches must be uint8 (got {})'.format(a.dtype))
+    return np.ascontiguousarray(a)
+
+
+class HostPipeline:
+    """Pinned-host hand-off around an :class:`Ensemble` (or :class:`Trial`): what replaces the Redis
+    lists of rafiki/cache/cache.py:36-63 between the predictor and co-located workers.
+
+    ``serve(batch) -> float32 numpy [n, C]`` copies the uint8 frames from pinned host memory to the
+    device, resizes them on the GPU when the callers' frames are not the size the trials were
+    trained on (``input_shape``; Pillow-NEAREST, ``rfk_resize_decode_u8``: the reference's
+    ``resize_as_images``, rafiki/model/dataset.py:76-78), runs the engine, and copies the
+    probabilities back, all on one stream; with ``depth`` > 1 slots, ``submit``/``collect`` keep
+    several batches in flight so the copies of one batch overlap the kernels of another.  Every slot
+    has its own stream, buffers AND kernel workspace, so slots never share scratch memory.
     """
 
-    def __init__(self, engine, max_batch, depth=2):
+    def __init__(self, engine, max_batch, depth=2, input_shape=None):
         _require_cuda()
         self.engine = engine
         self.device = engine.device
         self.max_batch = int(max_batch)
         self.depth = int(depth)
         d, c = engine.d, engine.n_classes
+        self.input_shape = tuple(int(v) for v in input_shape) if input_shape is not None else None
+        self._resize = None
+        d_host = d
+        if self.input_shape is not None:
+            s_in = self.input_shape[0]
+            ch = self.input_shape[2] if len(self.input_shape) == 3 else 1
+            if len(self.input_shape) < 2 or self.input_shape[1] != s_in:
+                raise ValueError('frames must be square: {}'.format(self.input_shape))
+            if engine.image_size is None or ch != engine.channels:
+                raise ValueError('frames {} do not match the trials ({} channels)'.format(self.input_shape, engine.channels))
+            if s_in != engine.image_size:
+                self._resize = (s_in, engine.image_size, ch)
+                d_host = s_in * s_in * ch
+        self.d_host = d_host
         self._slots = []
+        ws_bytes = max(engine.workspace_bytes(n) for n in {self.max_batch, min(self.max_batch, 128), 1})
         for _ in range(self.depth):
             self._slots.append({
-                'h_in': torch.empty((self.max_batch, d), dtype=torch.uint8).pin_memory(),
+                'h_in': torch.empty((self.max_batch, d_host), dtype=torch.uint8).pin_memory(),
                 'h_out': torch.empty((self.max_batch, c), dtype=torch.float32).pin_memory(),
+                'd_raw': (torch.empty((self.max_batch, d_host), dtype=torch.uint8, device=self.device)
+                          if self._resize else None),
                 'd_in': torch.empty((self.max_batch, d), dtype=torch.uint8, device=self.device),
                 'd_out': torch.empty((self.max_batch, c), dtype=torch.float32, device=self.device),
                 'stream': torch.cuda.Stream(device=self.device),
+                'ws': Workspace(self.device, ws_bytes),
                 'done': torch.cuda.Event(),
                 'n': 0,
             })
@@ -230,12 +305,15 @@ class HostPipeline:
         self.d2h_bytes = 0
 
     def stage(self, slot_idx, batch):
-        """Copy a ``uint8 [n, d]`` array into the slot's pinned input buffer (host -> host)."""
+        """Copy ``uint8`` frames (ndarray ``[n, ...]`` or bytes) into the slot's pinned input buffer."""
         s = self._slots[slot_idx]
-        n = batch.shape[0]
+        a = frames_as_uint8(batch, self.input_shape if self.input_shape is not None else (self.d_host,))
+        n = a.shape[0]
         if n > self.max_batch:
             raise ValueError('batch of {} exceeds max_batch {}'.format(n, self.max_batch))
-        s['h_in'][:n].copy_(torch.from_numpy(np.ascontiguousarray(batch).reshape(n, -1)))
+        if a.size != n * self.d_host:
+            raise ValueError('frames have {} bytes each, the pipeline expects {}'.format(a.size // max(n, 1), self.d_host))
+        s['h_in'][:n].copy_(torch.from_numpy(a.reshape(n, -1)))
         s['n'] = n
 
     def launch(self, slot_idx, n=None):
@@ -244,11 +322,17 @@ class HostPipeline:
         n = s['n'] if n is None else n
         s['n'] = n
         with torch.cuda.stream(s['stream']):
-            s['d_in'][:n].copy_(s['h_in'][:n], non_blocking=True)
-            self.engine.forward(s['d_in'][:n], out=s['d_out'][:n], stream=s['stream'])
+            if self._resize:
+                s_in, s_out, ch = self._resize
+                s['d_raw'][:n].copy_(s['h_in'][:n], non_blocking=True)
+                resize_decode_u8(s['d_raw'][:n].view((n, s_in, s_in) + ((ch,) if ch > 1 else ())), s_out,
+                                 out=s['d_in'][:n], stream=s['stream'])
+            else:
+                s['d_in'][:n].copy_(s['h_in'][:n], non_blocking=True)
+            self.engine.forward(s['d_in'][:n], out=s['d_out'][:n], stream=s['stream'], workspace=s['ws'])
             s['h_out'][:n].copy_(s['d_out'][:n], non_blocking=True)
             s['done'].record(s['stream'])
-        self.h2d_bytes = n * self.engine.d
+        self.h2d_bytes = n * self.d_host
         self.d2h_bytes = n * self.engine.n_classes * 4
 
     def wait(self, slot_idx):

@@ -240,6 +240,77 @@ def test_ensemble_forward(compute, tol, w, n):
         t.close()
 
 
+@pytest.mark.parametrize('w,n', [(3, 4096), (8, 1000), (2, 129)])
+def test_ensemble_forward_whole_tile_schedule(w, n, monkeypatch):
+    """The same small cases with the one-item-per-SM ("split") schedule switched off, so that they run
+    the schedule large batches run: a CTA takes whole tiles, all trials of a tile back to back, the
+    ensemble sum in registers.  Both schedules must give the same bits."""
+    dead = synth.dead_mask(784)
+    shapes = [(2, 128), (1, 36), (2, 7), (2, 128), (1, 128), (2, 64), (1, 2), (2, 100)]
+    params = [synth.make_trial(t, 28, 1, *shapes[t], dead=dead, data_kind='fashion') for t in range(w)]
+    X = synth.make_queries(n, 28, 1, 'fashion', seed=11, dead=dead)
+    x = torch.from_numpy(X).cuda()
+    trials = [engine.Trial(p) for p in params]
+    ens = engine.Ensemble(trials)
+    split = ens.forward(x).cpu().numpy()
+    monkeypatch.setenv('RFK_NO_SPLIT', '1')
+    whole = ens.forward(x).cpu().numpy()
+    monkeypatch.delenv('RFK_NO_SPLIT')
+    want = ff.ensemble_mean_array([ff.forward(p, X, np.float32) for p in params])
+    assert np.abs(whole.astype(np.float64) - want).max() <= TOL_TC
+    assert np.array_equal(whole, split)
+    for t in trials:
+        t.close()
+
+
+def test_whole_tile_schedule_heterogeneous_trials_batch_20000():
+    """Mid-size batch (157 tiles x 3 trials > 148 SMs: whole-tile schedule, several tiles per CTA)
+    with trials of different depth and width, against the oracle on every row."""
+    dead = synth.dead_mask(784)
+    params = [synth.make_trial(t, 28, 1, L, H, dead=dead, data_kind='fashion')
+              for t, (L, H) in enumerate([(2, 128), (1, 36), (2, 77)])]
+    X = synth.make_queries(20000, 28, 1, 'fashion', seed=21, dead=dead)
+    x = torch.from_numpy(X).cuda()
+    trials = [engine.Trial(p) for p in params]
+    got = engine.Ensemble(trials).forward(x).cpu().numpy()
+    want = ff.ensemble_mean_array([ff.forward(p, X, np.float32) for p in params])
+    assert np.abs(got.astype(np.float64) - want).max() <= TOL_TC
+    assert np.mean(got.argmax(1) == want.argmax(1)) >= 0.999
+    # equals "each trial alone, then kernel 3" bit for bit
+    singles = [t.forward(x) for t in trials]
+    assert np.array_equal(got, engine.ensemble_mean(singles).cpu().numpy())
+    for t in trials:
+        t.close()
+
+
+@pytest.mark.parametrize('n', [65536, 20000])
+def test_fused_kernel_gives_the_same_bits_on_every_launch(n):
+    """Row-independent predict (TfFeedForward.py:95) and a deterministic mean (ensemble.py:13-14):
+    the same batch launched again and again, alone and as W identical trials (whose float64 mean is
+    exact), must reproduce the first launch bit for bit.  (Round 1 failed this: two warps issued
+    the MMAs of one accumulator.)"""
+    dead = synth.dead_mask(784)
+    p = synth.make_trial(3, 28, 1, 2, 128, dead=dead)
+    x = torch.from_numpy(synth.make_queries(n, 28, 1, 'uniform', seed=5, dead=dead)).cuda()
+    tr = engine.Trial(p)
+    ref = tr.forward(x).clone()
+    side = torch.cuda.Stream()
+    junk = torch.empty(32 << 20, dtype=torch.uint8, device='cuda')
+    launches = 0
+    for w in (1, 2, 4, 8):
+        ens = engine.Ensemble([tr] * w)
+        for rep in range(6):
+            if rep & 1:                       # vary the load: a copy stream runs beside every other launch
+                with torch.cuda.stream(side):
+                    junk.copy_(junk.flip(0))
+            got = ens.forward(x)
+            launches += 1
+            assert torch.equal(got, ref), 'launch {} (w = {}) differs from the first'.format(launches, w)
+    assert launches >= 20
+    torch.cuda.synchronize()
+    tr.close()
+
+
 def test_full_size_properties_batch_65536():
     """BASELINE config 3 size: size-independent properties instead of an oracle pass."""
     dead = synth.dead_mask(784)

@@ -145,6 +145,39 @@ def test_failed_predict_does_not_hang_the_predictor(tmp_path, monkeypatch):
     t.join(2)
 
 
+def test_failed_predict_on_an_image_task_answers_none(tmp_path, monkeypatch):
+    """IMAGE_CLASSIFICATION: a worker whose predict() raised answers None; with no worker left the
+    predictor returns {'prediction': None} instead of pushing None rows into the mean."""
+    monkeypatch.chdir(tmp_path)
+    db, cache, workers = _deploy(tmp_path, [{'tag': 't0', 'boom': True}], task=TaskType.IMAGE_CLASSIFICATION)
+    w = workers[0]
+    with db:
+        (job, trial) = w._read_worker_info()
+        w._model = w._load_model(trial)
+        cache.add_worker_of_inference_job('worker-0', job)
+    pred = Predictor('predictor-svc', db=db, cache=cache)
+    pred.start()
+    t = threading.Thread(target=lambda: (w.step(timeout=1.0), w.step(timeout=1.0)), daemon=True)
+    t.start()
+    assert pred.predict([[0] * 28] * 28) == {'prediction': None}
+    assert pred.predict_batch([[[0] * 28] * 28] * 3) == {'predictions': [None, None, None]}
+    t.join(3)
+
+
+def test_binary_frames_ingress_without_gpu():
+    from rafiki_b200.engine import frames_as_uint8
+    a = np.arange(2 * 4 * 4, dtype=np.uint8).reshape(2, 4, 4)
+    assert frames_as_uint8(a) is a or np.shares_memory(frames_as_uint8(a), a)
+    b = frames_as_uint8(a.tobytes(), (4, 4))
+    assert b.shape == (2, 4, 4) and np.array_equal(a, b)
+    with pytest.raises(ValueError):
+        frames_as_uint8(b'12345', (2, 2))
+    with pytest.raises(ValueError):
+        frames_as_uint8(b'1234')
+    with pytest.raises(TypeError):
+        frames_as_uint8(np.zeros((1, 4, 4), np.float32))
+
+
 def test_plugin_contract_of_the_dropin_model_file():
     src = open(os.path.join(ROOT, 'examples', 'models', 'image_classification', 'TfFeedForward.py'), 'rb').read()
     cwd = os.getcwd()
