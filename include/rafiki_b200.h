@@ -49,6 +49,12 @@ typedef struct rfk_mlp rfk_mlp_t; /* one trial: packed TfFeedForward weights on 
 int rfk_version(void);
 const char* rfk_last_error(void);
 
+/* Launch accounting (no counterpart in the reference): how many kernels this library has launched
+ * in this process whose name contains `name_part` (NULL or "": all of them), e.g. "fused",
+ * "resize", "peer_reduce".  Lets a caller, a test or bench.py's `gpu_launches` count the CUDA
+ * work a call really did instead of assuming it. */
+unsigned long long rfk_launch_count(const char* name_part);
+
 /* 0 when `device` is a compute-capability 10.x GPU this library can run on. */
 int rfk_device_check(int device);
 
@@ -182,6 +188,42 @@ int rfk_peer_wait(const unsigned int* flags_of_this_rank, int world, unsigned in
  */
 int rfk_peer_signal(unsigned int* const* flags, int count, unsigned int step, void* stream);
 int rfk_peer_wait_flags(const unsigned int* flags, int count, unsigned int step, void* stream);
+
+/*
+ * One call per serving step of the trial-per-GPU ensemble (BASELINE configs[2]).
+ * Replaces: one Predictor.predict round -- the same queries pushed to every worker
+ * (rafiki/predictor/predictor.py:39-41), one answer gathered per worker and averaged
+ * (predictor.py:46-70) -- for one-process-per-GPU ranks of one box.
+ *
+ * rfk_peer_t holds every rank's mapped block, the block layout and the step counters.  Set-up:
+ * each rank allocates rfk_peer_block_bytes(...) with rfk_peer_alloc, the 64-byte handles are
+ * exchanged by the host (torch.distributed in the Python layer), every rank maps the others with
+ * rfk_peer_open and passes the `world` base pointers (its own at [rank]) to rfk_peer_create.
+ *
+ * Queries, in place of the reference's per-worker RPUSH of the same JSON query
+ * (rafiki/cache/cache.py:36-45): rank r uploads only rows rfk_peer_slice_rows(n, world, r) of the
+ * uint8 batch over its own PCIe link, to the address rfk_peer_upload_slot returns, and
+ * rfk_peer_allgather_u8 (every rank, same n, stream-ordered after the upload) pulls the other
+ * slices over NVLink; *gathered is then the whole batch on this device.
+ *
+ * rfk_peer_ensemble_step (every rank, same n) enqueues: this rank's fused trial kernel on `x`
+ * (w may be 0: the rank contributes zeros) -> the peer-memory reduce of the partial means ->
+ * on the root, the wait for all slices.  *result is the root's mean for this step (valid on
+ * the root once `stream` has passed the call).  Buffers alternate by step parity: a result
+ * must be consumed (on `stream`) before the step after next is enqueued.  All ranks must make
+ * the same sequence of calls; every wait inside is bounded (a dead rank makes the others trap).
+ */
+typedef struct rfk_peer rfk_peer_t;
+int rfk_peer_block_bytes(int world, int64_t max_n, int d, int n_classes, size_t* out);
+int rfk_peer_slice_rows(int64_t n, int world, int rank, int64_t* row_lo, int64_t* row_hi);
+int rfk_peer_create(rfk_peer_t** out, int world, int rank, int root, void* const* bases,
+                    int64_t max_n, int d, int n_classes);
+int rfk_peer_destroy(rfk_peer_t* p);
+int rfk_peer_upload_slot(rfk_peer_t* p, int64_t n, uint8_t** dst, int64_t* row_lo, int64_t* row_hi);
+int rfk_peer_allgather_u8(rfk_peer_t* p, int64_t n, const uint8_t** gathered, void* stream);
+int rfk_peer_ensemble_step(rfk_peer_t* p, rfk_mlp_t* const* trials, int w, int total_trials,
+                           const uint8_t* x, int64_t n, void* workspace, size_t workspace_bytes,
+                           float** result, void* stream);
 
 #ifdef __cplusplus
 }

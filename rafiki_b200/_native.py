@@ -35,6 +35,7 @@ _vp, _i, _i64, _sz, _f = _c.c_void_p, _c.c_int, _c.c_int64, _c.c_size_t, _c.c_fl
 PROTOTYPES = {
     'rfk_version': (_i, []),
     'rfk_last_error': (_c.c_char_p, []),
+    'rfk_launch_count': (_c.c_ulonglong, [_c.c_char_p]),
     'rfk_device_check': (_i, [_i]),
     'rfk_decode_u8': (_i, [_vp, _vp, _i64, _i, _i, _vp, _vp, _i, _vp]),
     'rfk_resize_decode_u8': (_i, [_vp, _vp, _i64, _i, _i, _i, _i, _vp, _vp, _i, _vp]),
@@ -58,7 +59,19 @@ PROTOTYPES = {
     'rfk_peer_wait': (_i, [_vp, _i, _c.c_uint, _vp]),
     'rfk_peer_signal': (_i, [_c.POINTER(_vp), _i, _c.c_uint, _vp]),
     'rfk_peer_wait_flags': (_i, [_vp, _i, _c.c_uint, _vp]),
+    'rfk_peer_block_bytes': (_i, [_i, _i64, _i, _i, _c.POINTER(_sz)]),
+    'rfk_peer_slice_rows': (_i, [_i64, _i, _i, _c.POINTER(_i64), _c.POINTER(_i64)]),
+    'rfk_peer_create': (_i, [_c.POINTER(_vp), _i, _i, _i, _c.POINTER(_vp), _i64, _i, _i]),
+    'rfk_peer_destroy': (_i, [_vp]),
+    'rfk_peer_upload_slot': (_i, [_vp, _i64, _c.POINTER(_vp), _c.POINTER(_i64), _c.POINTER(_i64)]),
+    'rfk_peer_allgather_u8': (_i, [_vp, _i64, _c.POINTER(_vp), _vp]),
+    'rfk_peer_ensemble_step': (_i, [_vp, _c.POINTER(_vp), _i, _i, _vp, _i64, _vp, _sz, _c.POINTER(_vp), _vp]),
 }
+
+
+def launch_count(name_part=None):
+    """Kernels launched by the library in this process whose name contains ``name_part`` (all if None)."""
+    return int(load().rfk_launch_count(name_part.encode() if name_part else None))
 
 _lib = None
 

@@ -69,7 +69,9 @@ constexpr int KB = 128;         // K elements per pipeline step: two atoms, so t
                                 // (loader -> converter -> MMA issuer) carries eight MMAs instead of four
 constexpr int A_STAGES = 2;     // A operand ring: converted query tile, in TENSOR memory (64 columns per stage)
 constexpr int B_STAGES = 4;     // B operand ring: first-layer weight blocks in shared memory; deep, because a
-                                // 32 KB block takes 1000-1500 cycles to arrive from L2 under load
+                                // 32 KB block takes 1000-1500 cycles to arrive from L2 under load.  (Eight
+                                // stages of one 16 KB atom each, handed back after four MMAs, measured 17 %
+                                // slower: the copies, not their latency, are what the ring waits for.)
 constexpr int RAW_STAGES = 3;   // raw uint8 ring (TMA landing zone; covers HBM latency)
 constexpr int HMAX = 128;       // widest hidden layer the fused path takes
 constexpr int CPAD = 16;        // class dimension padded to one UMMA N step
@@ -104,7 +106,15 @@ constexpr int kEpiThreads = kEpiWarps * 32;                   // 256
 constexpr int kConvThreads = kConvWarps * 32;                 // 256: half a row (64 bytes) per thread per step
 constexpr int kThreads = (kEpiWarps + kConvWarps + 4) * 32;   // 640
 constexpr int WARP_LOAD = kEpiWarps + kConvWarps, WARP_MMA = WARP_LOAD + 1, WARP_TAIL = WARP_LOAD + 3;
-constexpr int kRegsEpi = 136, kRegsLight = 56;
+constexpr int kRegsLaunch = 96;   // registers per thread the kernel is compiled for and launched with
+constexpr int kRegsEpi = 136, kRegsConv = 72, kRegsLight = 56;
+// setmaxnreg.inc only hands out what the CTA's own warps have given back: the pool is the launch
+// allocation, not the register file (an over-subscribed budget leaves one epilogue warp blocked for ever)
+static_assert(kEpiWarps * kRegsEpi + kConvWarps * kRegsConv + 4 * kRegsLight <= (kEpiWarps + kConvWarps + 4) * kRegsLaunch,
+              "setmaxnreg budget exceeds the launch allocation");
+// named barriers (id 0 is __syncthreads): the four softmax warps; converters -> layer-1 issuer, one per A stage;
+// epilogue warps -> layers-2/3 issuer
+constexpr int BAR_SOFTMAX = 1, BAR_A0 = 2 /* .. BAR_A0 + A_STAGES - 1 */, BAR_HID = BAR_A0 + 4;
 
 constexpr int TMEM_COLS = 512;
 constexpr int COL_ACC1 = 0;     // two buffers of 128 columns; layer 2 accumulates into the buffer its own
@@ -238,6 +248,15 @@ __device__ __forceinline__ void epilogue_hidden(uint32_t tmem_row_addr, int c_be
   tmem_st_wait();
 }
 
+// Hardware named barriers (bar.sync / bar.arrive): producers arrive without blocking, the consumer
+// syncs; `threads` counts both sides and is a multiple of 32.  Every lane of a warp executes them.
+__device__ __forceinline__ void named_bar_arrive(int id, int threads) {
+  asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
+__device__ __forceinline__ void named_bar_sync(int id, int threads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
+
 // One arrival per warp instead of one per thread: 32 arrivals on one mbarrier serialise in the
 // shared-memory atomic unit (~1 lane per cycle).  __syncwarp orders the lanes' earlier writes
 // (and their proxy / tcgen05 fences) before the elected lane's release-arrive.
@@ -302,7 +321,6 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
   }
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < A_STAGES; ++s) mbar_init(&bars->a_full[s], kConvWarps);
     for (int s = 0; s < B_STAGES; ++s) {
       mbar_init(&bars->b_full[s], 1);
       mbar_init(&bars->step_done[s], 1);
@@ -317,7 +335,6 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
       mbar_init(&bars->bias_full[b], 1);
       mbar_init(&bars->bias_free[b], kEpiWarps);
     }
-    mbar_init(&bars->hid_ready, kEpiWarps);
     mbar_init(&bars->acc2_full, 1);
     mbar_init(&bars->acc3_full, 1);
     mbar_init(&bars->w2_full, 1);
@@ -404,7 +421,7 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
             if (j < C) stage[row * C + j] = (float)(acc[j] / (double)(P.split ? 1 : P.total_trials));
 #pragma unroll
           for (int j = 0; j < CPAD; ++j) acc[j] = 0.0;
-          asm volatile("bar.sync 1, 128;" ::: "memory");           // the four softmax warps
+          named_bar_sync(BAR_SOFTMAX, 128);                       // the four softmax warps
           {
             const long long first = (long long)prev_tile * TILE_M;
             const long long rows = P.n - first < TILE_M ? P.n - first : TILE_M;
@@ -419,7 +436,7 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
               for (int i = row; i < valid; i += 128) o[i] = stage[i];
             }
           }
-          asm volatile("bar.sync 1, 128;" ::: "memory");           // staging buffer free again
+          named_bar_sync(BAR_SOFTMAX, 128);                       // staging buffer free again
         }
       } else {
         warp_arrive(&bars->bias_free[prev_buf]);
@@ -463,10 +480,8 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
         }
         tc_fence_before_sync();
         // two-hidden-layer items keep the accumulator: layer 2 accumulates into it (see below)
-        if (T.n_hidden == 2)
-          warp_arrive(&bars->hid_ready);
-        else
-          warp_arrive2(&bars->acc1_empty[buf], &bars->hid_ready);
+        named_bar_arrive(BAR_HID, kEpiThreads + 32);
+        if (T.n_hidden != 2) warp_arrive(&bars->acc1_empty[buf]);
         if (warp == 0) RFK_TRACE(3, 2);
         // ---- deferred softmax of the previous item, overlapping this item's layer-2 MMAs
         if (have_prev) finish_prev();
@@ -481,7 +496,8 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
           epilogue_hidden<kF16>(lane_addr + COL_ACC1 + buf * HMAX, half ? split : 0, half ? T.h2_pad : split, bias + HMAX,
                                 1.0f, hid_row_addr);
           tc_fence_before_sync();
-          warp_arrive2(&bars->acc1_empty[buf], &bars->hid_ready);
+          named_bar_arrive(BAR_HID, kEpiThreads + 32);
+          warp_arrive(&bars->acc1_empty[buf]);
           if (warp == 0) RFK_TRACE(3, 4);
         }
         have_prev = true;
@@ -504,7 +520,7 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
     // the row, warp / 4 = which 64 bytes): 4 x LDS.128, 32 exact conversions, and the 64 operand
     // values go straight into TENSOR memory (tcgen05.st), where the layer-1 MMAs read their A
     // operand -- the converted tile never touches shared memory.
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsLight));
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsConv));
     const int quarter = warp & 3;
     const int khalf = (warp - kEpiWarps) >> 2;
     const int row = quarter * 32 + lane;
@@ -520,36 +536,45 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
     for (int tile = tile0; tile < P.n_tiles; tile += tile_step) {
       for (int t = t0; t < t1; ++t) {
         for (int kb = 0; kb < n_kb; ++kb, ++gs) {
-          mbar_wait(&bars->raw_full[rstage], rphase);
-          // A stage gs % 2 was last read by the MMAs of step gs - 2
-          if (gs >= A_STAGES) mbar_wait(&bars->step_done[(gs - A_STAGES) % B_STAGES], (uint32_t)(((gs - A_STAGES) / B_STAGES) & 1));
-          if (warp == kEpiWarps) RFK_TRACE(0, 1);
-          tc_fence_after_sync();
           // 16-byte chunks of this thread's half row that the MMAs will read (the row may end inside the step)
           int live = (P.d - kb * KB - khalf * 64 + 15) >> 4;
           live = (P.debug & 2) ? 0 : (live < 0 ? 0 : (live > 4 ? 4 : live));
+          // (1) raw bytes -> operand pairs in registers, as soon as the raw tile has landed: the A stage
+          //     may still be in use by the MMAs of step gs - A_STAGES, so nothing is stored yet
+          mbar_wait(&bars->raw_full[rstage], rphase);
+          if (warp == kEpiWarps) RFK_TRACE(0, 1);
           const uint32_t rsrc = (uint32_t)rstage * RAW_STAGE;
-          const uint32_t dst = a_dst0 + (uint32_t)(gs % A_STAGES) * (KB / 2);
+          uint32_t p[32];
 #pragma unroll
           for (int h2 = 0; h2 < 2; ++h2) {
             if (live > 2 * h2) {                   // warp-uniform
               const uint4 r0 = lds_u4(raw_chunk[2 * h2] + rsrc), r1 = lds_u4(raw_chunk[2 * h2 + 1] + rsrc);
-              uint32_t p[16];
-              p[0] = u8x2_to_op<kF16>(r0.x, 0);  p[1] = u8x2_to_op<kF16>(r0.x, 2);
-              p[2] = u8x2_to_op<kF16>(r0.y, 0);  p[3] = u8x2_to_op<kF16>(r0.y, 2);
-              p[4] = u8x2_to_op<kF16>(r0.z, 0);  p[5] = u8x2_to_op<kF16>(r0.z, 2);
-              p[6] = u8x2_to_op<kF16>(r0.w, 0);  p[7] = u8x2_to_op<kF16>(r0.w, 2);
-              p[8] = u8x2_to_op<kF16>(r1.x, 0);  p[9] = u8x2_to_op<kF16>(r1.x, 2);
-              p[10] = u8x2_to_op<kF16>(r1.y, 0); p[11] = u8x2_to_op<kF16>(r1.y, 2);
-              p[12] = u8x2_to_op<kF16>(r1.z, 0); p[13] = u8x2_to_op<kF16>(r1.z, 2);
-              p[14] = u8x2_to_op<kF16>(r1.w, 0); p[15] = u8x2_to_op<kF16>(r1.w, 2);
-              tmem_st16(dst + 16u * h2, p);
+              uint32_t* q = p + 16 * h2;
+              q[0] = u8x2_to_op<kF16>(r0.x, 0);  q[1] = u8x2_to_op<kF16>(r0.x, 2);
+              q[2] = u8x2_to_op<kF16>(r0.y, 0);  q[3] = u8x2_to_op<kF16>(r0.y, 2);
+              q[4] = u8x2_to_op<kF16>(r0.z, 0);  q[5] = u8x2_to_op<kF16>(r0.z, 2);
+              q[6] = u8x2_to_op<kF16>(r0.w, 0);  q[7] = u8x2_to_op<kF16>(r0.w, 2);
+              q[8] = u8x2_to_op<kF16>(r1.x, 0);  q[9] = u8x2_to_op<kF16>(r1.x, 2);
+              q[10] = u8x2_to_op<kF16>(r1.y, 0); q[11] = u8x2_to_op<kF16>(r1.y, 2);
+              q[12] = u8x2_to_op<kF16>(r1.z, 0); q[13] = u8x2_to_op<kF16>(r1.z, 2);
+              q[14] = u8x2_to_op<kF16>(r1.w, 0); q[15] = u8x2_to_op<kF16>(r1.w, 2);
             }
           }
+          // the raw slot is free as soon as its bytes sit in registers (the conversions above consumed the loads)
+          warp_arrive(&bars->raw_empty[rstage]);
+          // (2) A stage gs % A_STAGES was last read by the MMAs of step gs - A_STAGES
+          if (gs >= A_STAGES) mbar_wait(&bars->step_done[(gs - A_STAGES) % B_STAGES], (uint32_t)(((gs - A_STAGES) / B_STAGES) & 1));
           if (warp == kEpiWarps) RFK_TRACE(0, 2);
+          tc_fence_after_sync();
+          const uint32_t dst = a_dst0 + (uint32_t)(gs % A_STAGES) * (KB / 2);
+#pragma unroll
+          for (int h2 = 0; h2 < 2; ++h2)
+            if (live > 2 * h2) tmem_st16(dst + 16u * h2, *reinterpret_cast<const uint32_t(*)[16]>(p + 16 * h2));
           tmem_st_wait();
           tc_fence_before_sync();
-          warp_arrive2(&bars->a_full[gs % A_STAGES], &bars->raw_empty[rstage]);
+          // (3) hand the stage to the issuer: a hardware named barrier (the issuer does bar.sync on the
+          //     same id) costs a few tens of cycles, an mbarrier arrive + waiter wake-up several hundred
+          named_bar_arrive(BAR_A0 + gs % A_STAGES, kConvThreads + 32);
           if (warp == kEpiWarps) RFK_TRACE(0, 3);
           if (++rstage == RAW_STAGES) { rstage = 0; rphase ^= 1u; }
         }
@@ -630,7 +655,6 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
         const uint32_t atom_bytes = (uint32_t)T.h1_pad * 128u;        // one 64-wide K atom of W1
         const uint8_t* src = T.w1;
         for (int kb = 0; kb < n_kb; ++kb) {
-          const uint32_t bytes = atom_bytes * (uint32_t)(n_atoms - 2 * kb < 2 ? n_atoms - 2 * kb : 2);
           wait_serving(&bars->raw_empty[rstage], rphase ^ 1u);
           RFK_TRACE(1, 1);
           if (P.debug & 32)
@@ -638,6 +662,7 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
           else
             tma_load_2d_expect_elect(smem + OFF_RAW + rstage * RAW_STAGE, &x_map, kb * KB, tile * TILE_M, RAW_STAGE,
                                      &bars->raw_full[rstage]);
+          const uint32_t bytes = atom_bytes * (uint32_t)(n_atoms - 2 * kb < 2 ? n_atoms - 2 * kb : 2);
           wait_serving(&bars->step_done[bstage], bphase ^ 1u);
           RFK_TRACE(1, 3);
           if (P.debug & 1)
@@ -670,7 +695,11 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
         for (int kb = 0; kb < n_kb; ++kb, ++gs) {
           const int as = gs % A_STAGES, bs = gs % B_STAGES;
           wait_prof<kProf>(&bars->b_full[bs], (uint32_t)((gs / B_STAGES) & 1), prof, PF_MMA_W23_FULL);
-          wait_prof<kProf>(&bars->a_full[as], (uint32_t)((gs / A_STAGES) & 1), prof, PF_MMA_FULL);
+          {
+            const long long tw = kProf ? clock64() : 0;
+            named_bar_sync(BAR_A0 + as, kConvThreads + 32);            // the converters have filled A stage `as`
+            if (kProf) prof[PF_MMA_FULL] += clock64() - tw;
+          }
           RFK_TRACE(2, 1);
           tc_fence_after_sync();
           if (!(P.debug & 4)) {
@@ -695,7 +724,6 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
     // hidden tile (A, written by the epilogue warps) x W2 / W3 (B, parameter loader).  A separate
     // warp, so that the layer-1 issuer never waits for an epilogue; the tensor pipe interleaves
     // the two instruction streams, which touch disjoint accumulators.
-    uint32_t hid_phase = 0;
     const uint32_t w2_lo = desc_lo_sw128(smem_base + OFF_W2), w3_lo = desc_lo_sw128(smem_base + OFF_W3);
     auto issue_small_layer = [&](uint32_t d_tmem, uint32_t b_lo, uint32_t b_atom, uint32_t idesc, int ksteps) {
       // A = hidden activations in tensor memory (8 columns per K step); B in 64-wide atoms of 4 steps
@@ -713,9 +741,12 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
         if (T.n_hidden == 2) {
           if (w > 1 || n2 == 0) wait_prof<kProf>(&bars->w2_full, (uint32_t)(n2 & 1), prof, PF_MMA_W23_FULL);
           ++n2;
-          wait_prof<kProf>(&bars->hid_ready, hid_phase, prof, PF_MMA_HID_L2);
+          {
+            const long long tw = kProf ? clock64() : 0;
+            named_bar_sync(BAR_HID, kEpiThreads + 32);
+            if (kProf) prof[PF_MMA_HID_L2] += clock64() - tw;
+          }
           RFK_TRACE(4, 1);
-          hid_phase ^= 1u;
           tc_fence_after_sync();
           issue_small_layer(tmem_base + COL_ACC1 + (uint32_t)buf * HMAX, w2_lo, ((uint32_t)T.h2_pad * 128u) >> 4,
                             idesc_16bit_f32(kF16, TILE_M, T.h2_pad), T.h1_pad >> 4);
@@ -724,9 +755,12 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
           RFK_TRACE(4, 2);
         }
         if (w > 1 || item < 2) wait_prof<kProf>(&bars->w3_full[buf], (uint32_t)((item >> 1) & 1), prof, PF_MMA_W23_FULL);
-        wait_prof<kProf>(&bars->hid_ready, hid_phase, prof, PF_MMA_HID_L3);
+        {
+          const long long tw = kProf ? clock64() : 0;
+          named_bar_sync(BAR_HID, kEpiThreads + 32);
+          if (kProf) prof[PF_MMA_HID_L3] += clock64() - tw;
+        }
         RFK_TRACE(4, 3);
-        hid_phase ^= 1u;
         tc_fence_after_sync();
         const int hl_pad = T.n_hidden == 2 ? T.h2_pad : T.h1_pad;
         issue_small_layer(tmem_base + COL_ACC3, w3_lo + (uint32_t)buf * (W3_BYTES >> 4), (CPAD * 128u) >> 4,
@@ -814,6 +848,16 @@ int fused_prepare(rfk_mlp* h) {
   s->dev.h2_pad = h->n_hidden == 2 ? h->layers[1].out_pad : 0;
   s->dev.n_hidden = h->n_hidden;
   s->dev.pad_ = 0;
+  {
+    // the setmaxnreg budget above assumes the registers the compiler really gave the kernel
+    cudaFuncAttributes fa;
+    RFK_CUDA_TRY(cudaFuncGetAttributes(&fa, fused_ensemble_kernel<true, false>));
+    if (fa.numRegs * (kEpiWarps + kConvWarps + 4) < kEpiWarps * kRegsEpi + kConvWarps * kRegsConv + 4 * kRegsLight) {
+      set_error("fused kernel was compiled with %d registers per thread; its setmaxnreg budget needs %d", fa.numRegs,
+                kRegsLaunch);
+      return RFK_ERR_UNSUPPORTED;
+    }
+  }
   static bool attr_set[64] = {false};
   if (!attr_set[h->device & 63]) {
     RFK_CUDA_TRY(cudaFuncSetAttribute(fused_ensemble_kernel<true, false>,

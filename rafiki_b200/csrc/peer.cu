@@ -231,3 +231,214 @@ extern "C" int rfk_peer_wait(const unsigned int* flags_of_this_rank, int world, 
   RFK_LAUNCH_CHECK("peer_wait_kernel");
   return RFK_OK;
 }
+
+
+// =========================================================================================
+// One call per serving step (trial-per-GPU ensemble, BASELINE configs[2]).
+//
+// The host loop of round 1 made three ctypes calls and kept the step counter in Python; at eight
+// ranks the Python per step was as long as the kernels.  rfk_peer_t holds the mapped blocks of
+// every rank, the layout and the step counters, so that one C call enqueues a whole step:
+//   [all-gather of the uint8 query slices over NVLink]  ->  fused trial kernel  ->  cross-rank mean.
+// Block layout (the same on every rank, so each rank can compute every peer's addresses):
+//   partial[2] | result[2] | queries[2] | flags
+// where partial / result hold max_n * n_classes floats, queries max_n * d bytes, all rounded up to
+// 256 bytes, and flags = 3 * world + 1 uint32: [0,G) "partials ready", [G,2G) "slice in place",
+// [2G] block counter, [2G+1, 3G+1) "query slice ready".
+namespace {
+
+struct PeerLayout {
+  size_t buf_bytes, x_bytes, off_partial[2], off_result[2], off_x[2], off_flags, total;
+};
+
+PeerLayout peer_layout(int world, int64_t max_n, int d, int n_classes) {
+  PeerLayout L;
+  L.buf_bytes = ((size_t)max_n * (size_t)n_classes * sizeof(float) + 255) / 256 * 256;
+  L.x_bytes = ((size_t)max_n * (size_t)d + 255) / 256 * 256;
+  size_t off = 0;
+  for (int k = 0; k < 2; ++k) { L.off_partial[k] = off; off += L.buf_bytes; }
+  for (int k = 0; k < 2; ++k) { L.off_result[k] = off; off += L.buf_bytes; }
+  for (int k = 0; k < 2; ++k) { L.off_x[k] = off; off += L.x_bytes; }
+  L.off_flags = off;
+  off += ((size_t)(3 * world + 1) * sizeof(unsigned int) + 255) / 256 * 256;
+  L.total = off;
+  return L;
+}
+
+// rows [lo, hi) of the batch that rank r uploads; multiples of 16 rows so that every slice starts
+// 16-byte aligned whatever d is
+void slice_rows(int64_t n, int world, int r, int64_t* lo, int64_t* hi) {
+  const int64_t units = (n + 15) / 16;
+  int64_t a = units * r / world * 16, b = units * (r + 1) / world * 16;
+  *lo = a < n ? a : n;
+  *hi = b < n ? b : n;
+}
+
+struct GatherPtrs {
+  const uint8_t* x[kMaxRanks];       // query buffer (this step's parity) of every rank, peer mapped
+  unsigned int* flags[kMaxRanks];
+  long long lo[kMaxRanks], hi[kMaxRanks];   // byte range of every rank's slice
+};
+
+// All-gather of the query slices: rank r has uploaded bytes [lo_r, hi_r) of the batch into its own
+// buffer (stream-ordered before this kernel); it says so to every peer, waits for theirs, and pulls
+// the other G - 1 slices over NVLink into its own buffer with 16-byte loads.
+__global__ void __launch_bounds__(kThreads)
+peer_allgather_kernel(const GatherPtrs ptrs, uint8_t* __restrict__ mine_x, int world, int rank, unsigned int step) {
+  unsigned int* mine = ptrs.flags[rank];
+  const int f0 = 2 * world + 1;
+  if (blockIdx.x == 0 && threadIdx.x < world) {
+    __threadfence_system();
+    st_release_sys(ptrs.flags[threadIdx.x] + f0 + rank, step);
+  }
+  if (threadIdx.x < world) {
+    if (!spin_until_ge(mine + f0 + threadIdx.x, step)) {
+      printf("rafiki_b200: query all-gather timed out waiting for rank %d (rank %d, step %u)\n", (int)threadIdx.x, rank, step);
+      __trap();
+    }
+  }
+  __syncthreads();
+  const long long stride = (long long)gridDim.x * kThreads * 16;
+  for (int jj = 1; jj < world; ++jj) {
+    const int j = (rank + jj) % world;             // every rank starts with a different peer
+    const uint8_t* src = ptrs.x[j];
+    for (long long b = ptrs.lo[j] + ((long long)blockIdx.x * kThreads + threadIdx.x) * 16; b < ptrs.hi[j]; b += 4 * stride) {
+      uint4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (b + u * stride < ptrs.hi[j])
+          asm("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+              : "=r"(v[u].x), "=r"(v[u].y), "=r"(v[u].z), "=r"(v[u].w) : "l"(src + b + u * stride));
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (b + u * stride < ptrs.hi[j]) *reinterpret_cast<uint4*>(mine_x + b + u * stride) = v[u];
+    }
+  }
+}
+
+}  // namespace
+
+struct rfk_peer {
+  int world = 1, rank = 0, root = 0, device = 0, d = 0, n_classes = 0;
+  int64_t max_n = 0;
+  PeerLayout L;
+  uint8_t* base[kMaxRanks] = {nullptr};
+  unsigned int rstep = 0, gstep = 0;       // reduce / gather steps issued so far (the same on every rank)
+  int grid_blocks = 0;
+};
+
+extern "C" int rfk_peer_block_bytes(int world, int64_t max_n, int d, int n_classes, size_t* out) {
+  RFK_REQUIRE(out != nullptr && world >= 1 && world <= kMaxRanks && max_n >= 1 && d >= 1 && n_classes >= 1,
+              "peer_block_bytes: bad argument");
+  *out = peer_layout(world, max_n, d, n_classes).total;
+  return RFK_OK;
+}
+
+extern "C" int rfk_peer_slice_rows(int64_t n, int world, int rank, int64_t* row_lo, int64_t* row_hi) {
+  RFK_REQUIRE(row_lo != nullptr && row_hi != nullptr && n >= 0 && world >= 1 && rank >= 0 && rank < world,
+              "peer_slice_rows: bad argument");
+  slice_rows(n, world, rank, row_lo, row_hi);
+  return RFK_OK;
+}
+
+extern "C" int rfk_peer_create(rfk_peer_t** out, int world, int rank, int root, void* const* bases, int64_t max_n,
+                               int d, int n_classes) {
+  RFK_REQUIRE(out != nullptr && bases != nullptr, "peer_create: NULL argument");
+  RFK_REQUIRE(world >= 1 && world <= kMaxRanks && rank >= 0 && rank < world && root >= 0 && root < world,
+              "peer_create: bad world/rank/root %d/%d/%d", world, rank, root);
+  RFK_REQUIRE(max_n >= 1 && d >= 1 && n_classes >= 1 && (max_n * n_classes) % 4 == 0,
+              "peer_create: max_n * n_classes must be a positive multiple of 4");
+  rfk_peer* p = new rfk_peer();
+  p->world = world; p->rank = rank; p->root = root; p->d = d; p->n_classes = n_classes; p->max_n = max_n;
+  p->L = peer_layout(world, max_n, d, n_classes);
+  for (int j = 0; j < world; ++j) {
+    if (bases[j] == nullptr || (reinterpret_cast<uintptr_t>(bases[j]) & 255) != 0) {
+      delete p;
+      rfk::set_error("peer_create: block of rank %d is NULL or not 256-byte aligned", j);
+      return RFK_ERR_INVALID;
+    }
+    p->base[j] = static_cast<uint8_t*>(bases[j]);
+  }
+  if (cudaGetDevice(&p->device) != cudaSuccess) p->device = 0;
+  p->grid_blocks = rfk::num_sms();
+  *out = p;
+  return RFK_OK;
+}
+
+extern "C" int rfk_peer_destroy(rfk_peer_t* p) {
+  delete p;
+  return RFK_OK;
+}
+
+extern "C" int rfk_peer_upload_slot(rfk_peer_t* p, int64_t n, uint8_t** dst, int64_t* row_lo, int64_t* row_hi) {
+  RFK_REQUIRE(p != nullptr && dst != nullptr && row_lo != nullptr && row_hi != nullptr, "peer_upload_slot: NULL argument");
+  RFK_REQUIRE(n >= 1 && n <= p->max_n, "peer_upload_slot: n %lld outside 1..%lld", (long long)n, (long long)p->max_n);
+  slice_rows(n, p->world, p->rank, row_lo, row_hi);
+  const int k = (int)((p->gstep + 1) & 1);
+  *dst = p->base[p->rank] + p->L.off_x[k] + (size_t)*row_lo * (size_t)p->d;
+  return RFK_OK;
+}
+
+extern "C" int rfk_peer_allgather_u8(rfk_peer_t* p, int64_t n, const uint8_t** gathered, void* stream) {
+  RFK_REQUIRE(p != nullptr, "peer_allgather: NULL argument");
+  RFK_REQUIRE(n >= 1 && n <= p->max_n, "peer_allgather: n %lld outside 1..%lld", (long long)n, (long long)p->max_n);
+  const unsigned int step = ++p->gstep;
+  const int k = (int)(step & 1);
+  GatherPtrs g;
+  for (int j = 0; j < kMaxRanks; ++j) {
+    g.x[j] = nullptr; g.flags[j] = nullptr; g.lo[j] = g.hi[j] = 0;
+    if (j < p->world) {
+      int64_t lo, hi;
+      slice_rows(n, p->world, j, &lo, &hi);
+      g.x[j] = p->base[j] + p->L.off_x[k];
+      g.flags[j] = reinterpret_cast<unsigned int*>(p->base[j] + p->L.off_flags);
+      g.lo[j] = lo * p->d;
+      g.hi[j] = hi * p->d;
+      // slices start at multiples of 16 rows, hence 16-byte aligned; a ragged end is rounded up
+      // inside the buffer (x_bytes is padded to 256)
+      g.hi[j] = (g.hi[j] + 15) / 16 * 16;
+    }
+  }
+  uint8_t* mine = p->base[p->rank] + p->L.off_x[k];
+  peer_allgather_kernel<<<p->grid_blocks, kThreads, 0, reinterpret_cast<cudaStream_t>(stream)>>>(g, mine, p->world,
+                                                                                               p->rank, step);
+  RFK_LAUNCH_CHECK("peer_allgather_kernel");
+  if (gathered != nullptr) *gathered = mine;
+  return RFK_OK;
+}
+
+extern "C" int rfk_peer_ensemble_step(rfk_peer_t* p, rfk_mlp_t* const* trials, int w, int total_trials,
+                                      const uint8_t* x, int64_t n, void* workspace, size_t workspace_bytes,
+                                      float** result, void* stream) {
+  RFK_REQUIRE(p != nullptr, "peer_ensemble_step: NULL argument");
+  RFK_REQUIRE(n >= 1 && n <= p->max_n && (n * p->n_classes) % 4 == 0,
+              "peer_ensemble_step: n %lld outside 1..%lld or n * classes not a multiple of 4", (long long)n,
+              (long long)p->max_n);
+  RFK_REQUIRE(x != nullptr, "peer_ensemble_step: x is NULL (pass the pointer rfk_peer_allgather_u8 returned)");
+  const unsigned int step = ++p->rstep;
+  const int k = (int)(step & 1);
+  float* partial = reinterpret_cast<float*>(p->base[p->rank] + p->L.off_partial[k]);
+  const int64_t count = n * p->n_classes;
+  if (w > 0) {
+    RFK_REQUIRE(trials != nullptr, "peer_ensemble_step: trials is NULL");
+    const int rc = rfk_ensemble_forward(trials, w, total_trials, x, n, partial, workspace, workspace_bytes, stream);
+    if (rc != RFK_OK) return rc;
+  } else {      // a rank that holds no trial (fewer trials than GPUs) contributes zeros
+    RFK_CUDA_TRY(cudaMemsetAsync(partial, 0, (size_t)count * sizeof(float), reinterpret_cast<cudaStream_t>(stream)));
+  }
+  const float* probs[kMaxRanks];
+  unsigned int* flags[kMaxRanks];
+  for (int j = 0; j < p->world; ++j) {
+    probs[j] = reinterpret_cast<const float*>(p->base[j] + p->L.off_partial[k]);
+    flags[j] = reinterpret_cast<unsigned int*>(p->base[j] + p->L.off_flags);
+  }
+  float* root_out = reinterpret_cast<float*>(p->base[p->root] + p->L.off_result[k]);
+  int rc = rfk_peer_reduce(probs, flags, p->world, p->rank, p->root, step, count, root_out, p->grid_blocks, stream);
+  if (rc != RFK_OK) return rc;
+  if (p->rank == p->root) {
+    rc = rfk_peer_wait(flags[p->rank], p->world, step, stream);
+    if (rc != RFK_OK) return rc;
+  }
+  if (result != nullptr) *result = reinterpret_cast<float*>(p->base[p->rank] + p->L.off_result[k]);
+  return RFK_OK;
+}

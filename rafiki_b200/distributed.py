@@ -34,7 +34,7 @@ class PeerReducer:
     the reduce-scatter-plus-gather kernel on every rank and, on the root, the wait for all slices.
     """
 
-    def __init__(self, n, n_classes, device, root=0, group=None, grid_blocks=148, overlap=False):
+    def __init__(self, n, n_classes, device, root=0, group=None, grid_blocks=148):
         from . import _native
         self._lib = _native.load()
         self._check = _native.check
@@ -47,11 +47,10 @@ class PeerReducer:
             raise ValueError('n * n_classes must be a multiple of 4 for the peer reduce')
         self.grid_blocks = int(grid_blocks)
         self.step = 0
-        # the reduce runs on its own stream so that it overlaps the next batch's fused kernel
-        self.overlap = bool(overlap)
-        self._side = torch.cuda.Stream(device=self.device) if self.overlap else None
-        self._ev_ready = [torch.cuda.Event() for _ in range(2)]
-        self._ev_done = [torch.cuda.Event() for _ in range(2)]
+        # Everything of one rank runs on ONE stream: the fused kernel of step s+2 is then ordered
+        # after this rank's reduce of step s+1, which waited for every peer's "ready" of step s+1,
+        # which each peer raised after its own reduce of step s -- so nobody still reads the
+        # partials of step s when they are overwritten.  (A side-stream variant broke that chain.)
         # one block per rank: partial[0] | partial[1] | result[0] | result[1] | flags
         buf_bytes = (self.count * 4 + 255) // 256 * 256
         self._offsets = [0, buf_bytes, 2 * buf_bytes, 3 * buf_bytes, 4 * buf_bytes]
@@ -83,12 +82,12 @@ class PeerReducer:
         self._flags_ptr = self._base + self._offsets[4]
         dist.barrier(group=group)
 
-    def _as_tensor(self, ptr, shape):
-        """A float32 torch view of raw device memory owned by this object."""
+    def _as_tensor(self, ptr, shape, typestr='<f4', dtype=None):
+        """A torch view (float32 by default) of raw device memory owned by this object."""
         class _Holder:
             pass
         hld = _Holder()
-        hld.__cuda_array_interface__ = {'shape': tuple(shape), 'typestr': '<f4', 'data': (int(ptr), False), 'version': 2}
+        hld.__cuda_array_interface__ = {'shape': tuple(shape), 'typestr': typestr, 'data': (int(ptr), False), 'version': 2}
         hld.owner = self
         return torch.as_tensor(hld, device=self.device)
 
@@ -105,36 +104,24 @@ class PeerReducer:
     def next_partial(self):
         """The buffer this rank's fused kernel must write for the coming step.  (Its previous
         contents, two steps old, have been consumed: the current stream waits for that reduce.)"""
-        k = (self.step + 1) & 1
-        if self.overlap and self.step >= 2:
-            torch.cuda.current_stream(self.device).wait_event(self._ev_done[k])
-        return self.partial[k]
+        return self.partial[(self.step + 1) & 1]
 
     def reduce(self):
         """Enqueue the cross-rank mean of the buffers handed out by ``next_partial``; returns the
         result tensor (meaningful on the root, once the stream has passed this point)."""
         self.step += 1
         k = self.step & 1
-        cur = torch.cuda.current_stream(self.device)
-        run_on = self._side if self.overlap else cur
-        if self.overlap:
-            self._ev_ready[k].record(cur)               # the partials of this step are written
-            run_on.wait_event(self._ev_ready[k])
-        stream = ctypes.c_void_p(run_on.cuda_stream)
+        stream = ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
         if torch.cuda.current_device() != self.device.index:
             torch.cuda.set_device(self.device)       # one process per GPU: this rank only ever uses its own device
         self._check(self._lib.rfk_peer_reduce(self._probs_ptrs[k], self._flag_ptrs, self.world, self.rank, self.root,
                                               self.step, self.count, self._root_out[k], self.grid_blocks, stream))
         if self.rank == self.root:
             self._check(self._lib.rfk_peer_wait(self._flags_ptr, self.world, self.step, stream))
-        if self.overlap:
-            self._ev_done[k].record(run_on)
         return self.result[k]
 
     def wait(self, k=None):
-        """Make the current stream wait for the reduce of the last step (or of parity k)."""
-        if self.overlap:
-            torch.cuda.current_stream(self.device).wait_event(self._ev_done[self.step & 1 if k is None else k])
+        """Kept for callers of the earlier interface: the reduce runs on the calling stream."""
 
 
 class PeerGather(PeerReducer):
@@ -157,7 +144,6 @@ class PeerGather(PeerReducer):
         self.n, self.n_classes = int(n), int(n_classes)
         self.count = self.n * self.n_classes
         self.step = 0
-        self.overlap = False
         G = self.world
         buf_bytes = (self.count * 4 + 255) // 256 * 256
         self._buf_bytes = buf_bytes
@@ -217,6 +203,119 @@ class PeerGather(PeerReducer):
 
     def wait(self, k=None):
         pass
+
+
+def slice_rows(n, world_size, rank):
+    """Rows ``[lo, hi)`` of an ``n``-row batch that ``rank`` uploads (``rfk_peer_slice_rows``: slices
+    start at multiples of 16 rows so that every slice is 16-byte aligned for any row length)."""
+    if not (0 <= rank < world_size):
+        raise ValueError('rank {} outside world of {}'.format(rank, world_size))
+    units = (n + 15) // 16
+    return min(units * rank // world_size * 16, n), min(units * (rank + 1) // world_size * 16, n)
+
+
+class PeerEnsemble:
+    """The trial-per-GPU ensemble with ONE native call per step (``rfk_peer_ensemble_step``).
+
+    Mirrors one ``Predictor.predict`` round (rafiki/predictor/predictor.py:35-70) across ranks:
+    every rank holds some trials and sees every query; the mean over all trials lands on ``root``.
+    ``local`` is this rank's :class:`rafiki_b200.engine.Ensemble` (built with ``total_trials`` = all
+    trials) or ``None`` for a rank without a trial.
+
+    * ``step(x)``: fused kernel on the device-resident batch ``x`` -> peer-memory reduce -> (root)
+      wait; returns the root's result tensor.
+    * ``upload(batch_u8_pinned)`` + ``gather()``: each rank copies only ITS rows of the batch
+      from pinned host memory (its own PCIe link) and the other slices arrive over NVLink
+      (``rfk_peer_allgather_u8``); returns the whole batch on this device, ready for ``step``.
+    Everything is enqueued on the current stream; the host never synchronises.
+    """
+
+    def __init__(self, local, n_trials, max_n, d, n_classes, device, root=0, group=None):
+        from . import _native
+        self._lib = _native.load()
+        self._check = _native.check
+        self.local = local
+        self.n_trials = int(n_trials)
+        self.device = torch.device(device)
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        self.root = root
+        self.max_n, self.d, self.n_classes = int(max_n), int(d), int(n_classes)
+        nbytes = ctypes.c_size_t()
+        self._check(self._lib.rfk_peer_block_bytes(self.world, self.max_n, self.d, self.n_classes, ctypes.byref(nbytes)))
+        base = ctypes.c_void_p()
+        handle = ctypes.create_string_buffer(64)
+        with torch.cuda.device(self.device):
+            self._check(self._lib.rfk_peer_alloc(nbytes.value, ctypes.byref(base), handle))
+        self._base = base.value
+        everyone = [None] * self.world
+        dist.all_gather_object(everyone, (bytes(handle.raw), self.device.index), group=group)
+        bases, self._opened = [], []
+        with torch.cuda.device(self.device):      # map with MY device current: my kernels will touch it
+            for r, (h, peer_dev) in enumerate(everyone):
+                if r == self.rank:
+                    bases.append(self._base)
+                    continue
+                self._check(self._lib.rfk_peer_enable(int(peer_dev)))
+                p = ctypes.c_void_p()
+                self._check(self._lib.rfk_peer_open(ctypes.create_string_buffer(h, 64), ctypes.byref(p)))
+                bases.append(p.value)
+                self._opened.append(p.value)
+            ctx = ctypes.c_void_p()
+            arr = (ctypes.c_void_p * self.world)(*bases)
+            self._check(self._lib.rfk_peer_create(ctypes.byref(ctx), self.world, self.rank, self.root, arr,
+                                                  self.max_n, self.d, self.n_classes))
+        self._ctx = ctx.value
+        self._handles = local._handles if local is not None else None
+        self._w = len(local.trials) if local is not None else 0
+        self._ws = None
+        if local is not None:
+            from .engine import Workspace
+            self._ws = Workspace(self.device)
+        dist.barrier(group=group)
+
+    _as_tensor = PeerReducer._as_tensor
+
+    def close(self):
+        if getattr(self, '_base', None) is None:
+            return
+        torch.cuda.synchronize(self.device)
+        with torch.cuda.device(self.device):
+            self._lib.rfk_peer_destroy(self._ctx)
+            for p in self._opened:
+                self._lib.rfk_peer_close(p)
+            self._lib.rfk_peer_free(self._base)
+        self._base = None
+
+    def upload(self, host_batch):
+        """Enqueue the H2D copy of this rank's rows of ``host_batch`` (pinned ``uint8 [n, d]`` tensor)
+        into the slot the next ``gather`` reads.  Returns the number of bytes copied."""
+        n = host_batch.shape[0]
+        dst, lo, hi = ctypes.c_void_p(), ctypes.c_int64(), ctypes.c_int64()
+        self._check(self._lib.rfk_peer_upload_slot(self._ctx, n, ctypes.byref(dst), ctypes.byref(lo), ctypes.byref(hi)))
+        rows = hi.value - lo.value
+        if rows > 0:
+            view = self._as_tensor(dst.value, (rows, self.d), '|u1', torch.uint8)
+            view.copy_(host_batch[lo.value:hi.value].reshape(rows, self.d), non_blocking=True)
+        return rows * self.d
+
+    def gather(self, n):
+        """All-gather of the uploaded slices; returns the whole ``uint8 [n, d]`` batch on this device."""
+        out = ctypes.c_void_p()
+        stream = ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+        self._check(self._lib.rfk_peer_allgather_u8(self._ctx, n, ctypes.byref(out), stream))
+        return self._as_tensor(out.value, (n, self.d), '|u1', torch.uint8)
+
+    def step(self, x):
+        n = x.shape[0]
+        ws, ws_bytes = (ctypes.c_void_p(0), 0)
+        if self.local is not None:
+            ws, ws_bytes = self._ws.get(self.local.workspace_bytes(n))
+        res = ctypes.c_void_p()
+        stream = ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+        self._check(self._lib.rfk_peer_ensemble_step(self._ctx, self._handles, self._w, self.n_trials, x.data_ptr(), n,
+                                                     ws, ws_bytes, ctypes.byref(res), stream))
+        return self._as_tensor(res.value, (n, self.n_classes))
 
 
 class DistributedEnsemble:
