@@ -74,8 +74,9 @@ def make_workload(wl, rng_seed=0, n_batches=None):
 
 
 class ClockSampler(threading.Thread):
-    """SM clock and throttle reasons sampled during the timed region: NVML every 5 ms when the bindings
-    load (a timed region is tens of milliseconds), else nvidia-smi every 200 ms."""
+    """SM clock and throttle reasons sampled during the timed region: NVML every 50 ms when the bindings
+    load, else nvidia-smi every 200 ms.  Built and started BEFORE the warm-up on every rank (NVML
+    start-up costs milliseconds and must not sit between the barrier and the first timed step)."""
     QUERY = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
              'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
     NAMES = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
@@ -124,11 +125,26 @@ class ClockSampler(threading.Thread):
                     self._sample_smi()
             except Exception:
                 pass
-            self._halt.wait(0.005 if self._nvml is not None else 0.2)
+            self._halt.wait(0.05 if self._nvml is not None else 0.2)
+
+    def mark(self):
+        """Samples taken before this call (warm-up) are dropped from the summary."""
+        self._from = len(self.samples)
+        try:
+            if self._nvml is not None:
+                self._sample_nvml()
+        except Exception:
+            pass
 
     def stop(self):
         self._halt.set()
         self.join(3)
+        try:
+            if self._nvml is not None:
+                self._sample_nvml()
+        except Exception:
+            pass
+        self.samples = self.samples[getattr(self, '_from', 0):]
         sm = [s[0] for s in self.samples]
         mx = [s[1] for s in self.samples if s[1] is not None]
         reasons = [n for i, n in enumerate(self.NAMES) if any(s[2][i] for s in self.samples)]
@@ -154,28 +170,33 @@ def cpu_oracle_rate(params, batch, sample, repeats, threads):
 
 
 def run_reference(args, wl):
+    """The reference arm: the CPU port of the reference path (the oracle; TensorFlow 1.12 cannot be
+    installed) on the box's host cores, list in / list out, a bounded sample of the batch per step."""
     rank = int(os.environ.get('RANK', '0'))
     if rank != 0:
         return 0
     params, batches, d = make_workload(wl, n_batches=1)
     cores = os.cpu_count() or 1
-    sample = min(wl['batch'], 512)     # bounded per-step sample: ~0.4 s of CPU work per step
-    for _ in range(max(args.warmup, 1) if args.warmup < 3 else 1):
+    sample = min(wl['batch'], int(os.environ.get('RFK_REFERENCE_SAMPLE', '512')))   # ~0.2-0.4 s of CPU work per step
+    for _ in range(max(1, min(args.warmup, 3))):
         cpu_oracle_rate(params, batches[0], min(sample, 256), 1, cores)
     t0 = time.perf_counter()
     for _ in range(args.steps):
         cpu_oracle_rate(params, batches[0], sample, 1, cores)
     dt = time.perf_counter() - t0
     value = sample * args.steps / dt
+    one_thread, _ = cpu_oracle_rate(params, batches[0], min(sample, 256), 1, 1)      # BLAS pinned to one thread
     line = {
         'impl': 'reference', 'metric': 'ensemble_queries_per_sec', 'value': value, 'unit': 'queries/s',
         'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': dt / args.steps * 1e3,
         'higher_is_better': True, 'scaling': wl['scaling'], 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-        'config': {'workload': wl['name'], 'trials': wl['trials'], 'batch': wl['batch'],
-                   'note': 'CPU oracle port of the reference path (TensorFlow 1.12 not installable); '
-                           'each step = first {} queries of the batch, list in / list out'.format(sample)},
+        'config': {'workload': wl['name'], 'trials': wl['trials'], 'batch': wl['batch'], 'sample_queries': sample,
+                   'note': 'CPU oracle port of the reference path (TensorFlow 1.12 not installable); the rate is per '
+                           'query, so each step runs the first {} queries of the {}-query batch through all {} trials '
+                           '(list in / list out), not the whole batch'.format(sample, wl['batch'], wl['trials'])},
         'cpu_baseline': {'value': value, 'unit': 'queries/s', 'cores': cores, 'kind': 'port',
-                         'sample': '{} queries x {} trials per step'.format(sample, wl['trials'])},
+                         'sample': '{} queries x {} trials per step'.format(sample, wl['trials']),
+                         'value_blas_1_thread': one_thread},
         'e2e': {'value': value, 'unit': 'queries/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
         'gpu_launches': 0,
     }
@@ -195,23 +216,28 @@ def run_latency_sweep(args, wl, ens, xs, out, params, rank):
         for i in range(20):
             ens.forward(x[i % len(x)], out=o)
         torch.cuda.synchronize()
-        lat = []
-        for i in range(max(args.steps, 200)):
+        lat, wall = [], []
+        for i in range(min(max(args.steps, 200), 400)):
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            t0 = time.perf_counter()
             a.record()
             ens.forward(x[i % len(x)], out=o)
             b.record()
             b.synchronize()
+            wall.append((time.perf_counter() - t0) * 1e3)
             lat.append(a.elapsed_time(b))
         lat.sort()
+        wall.sort()
         p50, p99 = lat[len(lat) // 2], lat[min(len(lat) - 1, int(len(lat) * 0.99))]
-        rows.append({'batch': bsz, 'p50_ms': p50, 'p99_ms': p99, 'queries_per_s_at_p50': bsz / (p50 * 1e-3)})
+        rows.append({'batch': bsz, 'p50_ms': p50, 'p99_ms': p99, 'queries_per_s_at_p50': bsz / (p50 * 1e-3),
+                     'host_wall_p50_ms': wall[len(wall) // 2], 'host_wall_p99_ms': wall[min(len(wall) - 1, int(len(wall) * 0.99))]})
     if rank == 0:
         cores = os.cpu_count() or 1
         cpu_rows = []
         if not args.no_cpu_baseline:
-            for bsz in (1, 32, 1024):
-                rate, times = cpu_oracle_rate(params, xs[0].cpu().numpy(), bsz, 3, cores)
+            host_batch = xs[0].cpu().numpy()
+            for bsz in (1, 32, 1024, 4096):
+                rate, times = cpu_oracle_rate(params, host_batch, bsz, 3 if bsz <= 1024 else 1, cores)
                 cpu_rows.append({'batch': bsz, 'ms': min(times) * 1e3, 'queries_per_s': rate})
         print(json.dumps({'metric': 'ensemble_batch_latency_ms', 'unit': 'ms', 'higher_is_better': False,
                           'n_gpus': 1, 'dtype': args.compute, 'data': 'synthetic',
@@ -269,25 +295,34 @@ def main():
         mine = [t for t in range(W) if t % world == rank]
     else:                              # independent replicas
         mine = list(range(W))
+    from rafiki_b200 import _native
     from rafiki_b200.distributed import DistributedEnsemble
+    sampler = ClockSampler(local_rank)        # every rank, before the warm-up
+    sampler.start()
     trials = [engine.Trial(params[t], compute=args.compute) for t in mine]
     ens = engine.Ensemble(trials, total_trials=W) if trials else None
     xs = [torch.from_numpy(b).to(dev) for b in batches]
     out = torch.zeros((n, C), dtype=torch.float32, device=dev)
     do_reduce = world > 1 and wl['scaling'] == 'strong' and wl.get('shard') != 'rows'
     dens = DistributedEnsemble(ens, W, C, dev, root=0) if do_reduce else None
-    reducer = None
-    if do_reduce and args.reduce in ('peer', 'gather'):
-        from rafiki_b200.distributed import PeerGather, PeerReducer
-        reducer = (PeerGather if args.reduce == 'gather' else PeerReducer)(n, C, dev, root=0)
+    reducer = peer = None
+    if do_reduce and args.reduce == 'peer':
+        from rafiki_b200.distributed import PeerEnsemble
+        peer = PeerEnsemble(ens, W, n, d, C, dev, root=0)       # one native call per step
+    elif do_reduce and args.reduce == 'gather':
+        from rafiki_b200.distributed import PeerGather
+        reducer = PeerGather(n, C, dev, root=0)
 
     outs = [out, torch.zeros_like(out)]
     pending = [None, None]
+    last = [None]
 
     def step(i):
-        if reducer is not None:
-            # local fused kernel, then kernel 3 fused with the collective over NVLink peer memory
-            dens.forward_peer(xs[i % len(xs)], reducer)
+        if peer is not None:
+            # fused kernel + kernel 3 fused with the collective over NVLink peer memory: one C call
+            last[0] = peer.step(xs[i % len(xs)])
+        elif reducer is not None:
+            last[0] = dens.forward_peer(xs[i % len(xs)], reducer)
         elif dens is not None:
             # local fused kernel + NCCL reduce onto rank 0; two result buffers in turn, so the
             # reduce of batch i overlaps the kernel of batch i+1
@@ -295,19 +330,18 @@ def main():
             if pending[slot] is not None:
                 pending[slot].wait()
             pending[slot] = dens.forward_async(xs[i % len(xs)], outs[slot])
+            last[0] = outs[slot]
         elif ens is not None:
-            ens.forward(xs[i % len(xs)], out=out)
+            last[0] = ens.forward(xs[i % len(xs)], out=out)
 
     def drain():
-        if reducer is not None:
-            reducer.wait(0)
-            reducer.wait(1)
         for k in range(2):
             if pending[k] is not None:
                 pending[k].wait()
                 pending[k] = None
 
     if wl.get('sweep'):
+        sampler.stop()
         return run_latency_sweep(args, wl, ens, xs, out, params, rank)
 
     def barrier():
@@ -315,27 +349,59 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    for i in range(max(args.warmup, 3)):
+    warm = max(args.warmup, 3)
+    for i in range(warm):
         step(i)
     drain()
     barrier()
-    sampler = ClockSampler(local_rank) if rank == 0 else None
-    if sampler:
-        sampler.start()
+    # rank skew from the barrier itself stays outside the timed region: a few synchronising steps
+    # (at N > 1 every step ends in a cross-rank hand-shake), then the events
+    if world > 1:
+        for i in range(5):
+            step(i)
+        drain()
+        torch.cuda.synchronize()
+        dist.barrier()
+    launches0 = _native.launch_count()
+    sampler.mark()
+    step_ev = [torch.cuda.Event(enable_timing=True) for _ in range(min(args.steps, 256) + 1)]
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
+    step_ev[0].record()
     for i in range(args.steps):
         step(i)
+        if i + 1 < len(step_ev):
+            step_ev[i + 1].record()
     drain()
     e1.record()
+    torch.cuda.synchronize()
+    launches = _native.launch_count() - launches0
+    clocks = sampler.stop()
     barrier()
     ms = e0.elapsed_time(e1)
+    per_step = sorted(step_ev[k].elapsed_time(step_ev[k + 1]) for k in range(len(step_ev) - 1))
+    ms_median_step = per_step[len(per_step) // 2]
     if world > 1:
-        t = torch.tensor([ms], device=dev)
+        t = torch.tensor([ms, ms_median_step], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
+        ms, ms_median_step = float(t[0].item()), float(t[1].item())
     units = (n_total if wl.get('shard') == 'rows' else n) * args.steps * (world if wl['scaling'] == 'weak' else 1)
     value = units / (ms * 1e-3)
+
+    # ---- the N > 1 result against the single-GPU ensemble of the same batch (rank 0 holds all parameters)
+    parity = None
+    if do_reduce:
+        step(0)
+        drain()
+        torch.cuda.synchronize()
+        dist.barrier()
+        if rank == 0:
+            full = [engine.Trial(params[t], compute=args.compute) for t in range(W)]
+            want = engine.Ensemble(full).forward(xs[0])
+            parity = float((last[0].double() - want.double()).abs().max().item())
+            for t in full:
+                t.close()
+        dist.barrier()
 
     # ---- per-batch latency (the metric's "p99 batch latency"): one step at a time, device timed
     lat = []
@@ -353,7 +419,59 @@ def main():
 
     # ---- end to end: pinned host -> device -> pinned host, three batches in flight
     e2e = None
-    if dens is not None:
+    if peer is not None:
+        # rank r: ITS rows of the batch, pinned host -> device over its own PCIe link (copy stream, overlapping
+        # the previous step's kernels); all-gather of the slices over NVLink; fused kernel; peer reduce;
+        # rank 0: probabilities -> pinned host
+        h_in = torch.from_numpy(batches[0]).pin_memory()
+        h_out = torch.empty((n, C), dtype=torch.float32).pin_memory()
+        e2e_steps = max(4, min(args.steps, 40))
+        cur = torch.cuda.current_stream()
+        copy = torch.cuda.Stream(device=dev)
+        ev_up = [torch.cuda.Event(), torch.cuda.Event()]
+        ev_g = torch.cuda.Event()
+        up_bytes = 0
+
+        def upload(k):
+            nonlocal up_bytes
+            copy.wait_event(ev_g)
+            with torch.cuda.stream(copy):
+                up_bytes = peer.upload(h_in)
+                ev_up[k].record(copy)
+
+        ev_g.record(cur)
+        upload(0)
+        t0 = None
+        for it in range(3 + e2e_steps):
+            if it == 3:
+                barrier()
+                t0 = time.perf_counter()
+            cur.wait_event(ev_up[it & 1])
+            xg = peer.gather(n)
+            ev_g.record(cur)
+            upload((it + 1) & 1)                 # next step's slice while this step computes
+            res = peer.step(xg)
+            if rank == 0:
+                h_out.copy_(res, non_blocking=True)
+        barrier()
+        dt = time.perf_counter() - t0
+        t = torch.tensor([dt, float(up_bytes)], device=dev)
+        dist.all_reduce(t[:1], op=dist.ReduceOp.MAX)
+        dist.all_reduce(t[1:], op=dist.ReduceOp.SUM)
+        dt = float(t[0].item())
+        e2e_parity = None
+        if rank == 0:
+            full = [engine.Trial(params[t_], compute=args.compute) for t_ in range(W)]
+            want = engine.Ensemble(full).forward(xs[0])
+            e2e_parity = float((torch.from_numpy(h_out.numpy()).to(dev).double() - want.double()).abs().max().item())
+            for t_ in full:
+                t_.close()
+        e2e = {'value': n * e2e_steps / dt, 'unit': 'queries/s', 'h2d_bytes_per_step': int(t[1].item()),
+               'd2h_bytes_per_step': n * C * 4, 'steps': e2e_steps, 'parity_vs_single_gpu': e2e_parity,
+               'note': 'each rank uploads only its 1/N of the rows from pinned host memory (own PCIe link, copy '
+                       'stream), the slices are all-gathered over NVLink peer memory (rfk_peer_allgather_u8), '
+                       'fused kernel, peer-memory reduce, rank 0 downloads the probabilities'}
+    elif dens is not None:
         # every rank: pinned host batch -> device -> fused kernel -> reduce; rank 0: result -> pinned host
         h_in = torch.from_numpy(batches[0]).pin_memory()
         d_in = torch.empty_like(xs[0])
@@ -365,8 +483,6 @@ def main():
                 t0 = time.perf_counter()
             d_in.copy_(h_in, non_blocking=True)
             res = dens.forward_peer(d_in, reducer) if reducer is not None else dens.forward(d_in, out=out)
-            if reducer is not None:
-                reducer.wait()
             if rank == 0:
                 h_out.copy_(res, non_blocking=True)
         barrier()
@@ -377,7 +493,8 @@ def main():
         e2e = {'value': n * e2e_steps / dt, 'unit': 'queries/s', 'h2d_bytes_per_step': n * d * world,
                'd2h_bytes_per_step': n * C * 4, 'steps': e2e_steps,
                'note': 'every rank uploads the whole uint8 batch from pinned host memory (its own PCIe link), '
-                       'fused kernel, NCCL reduce, rank 0 downloads the probabilities'}
+                       'fused kernel, {}, rank 0 downloads the probabilities'.format(
+                           'gather fused into the trial kernel' if reducer is not None else 'NCCL reduce')}
     elif ens is not None:
         depth = 3
         pipe = engine.HostPipeline(ens, max_batch=n, depth=depth)
@@ -408,7 +525,32 @@ def main():
         e2e = {'value': e_units / dt, 'unit': 'queries/s', 'h2d_bytes_per_step': pipe.h2d_bytes,
                'd2h_bytes_per_step': pipe.d2h_bytes, 'steps': e2e_steps, 'slots_in_flight': depth,
                'note': 'per rank: H2D of the whole uint8 batch + fused kernel + D2H of the probabilities'}
-    clocks = sampler.stop() if sampler else None
+    # ---- the drop-in's own API, N = 1: Predictor.predict_batch with a uint8 ndarray (binary ingress) and with the
+    #      reference's nested Python lists (what the CPU arm is fed), wall clock around the call
+    api = {}
+    if world == 1 and ens is not None and wl['channels'] == 1 and not wl.get('shard'):
+        from rafiki_b200.predictor import Predictor
+        pred = Predictor('bench-predictor', db=object())
+        pred.attach_ensemble(ens, max_batch=n)
+        S = wl['image_size']
+        frames = batches[0].reshape(n, S, S)
+        pred.predict_batch(frames)
+        reps = 5
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            got = pred.predict_batch(frames)['predictions']
+        dt = (time.perf_counter() - t0) / reps
+        api['e2e_ndarray_api'] = {'value': n / dt, 'unit': 'queries/s', 'batch': n, 'ms': dt * 1e3,
+                                  'what': 'Predictor.predict_batch(uint8 ndarray [n,28,28]) -> float32 ndarray, wall clock'}
+        m = min(n, 8192)
+        as_lists = frames[:m].tolist()
+        t0 = time.perf_counter()
+        got_l = pred.predict_batch(as_lists)['predictions']
+        dt = time.perf_counter() - t0
+        assert len(got_l) == m and abs(got_l[0][0] - float(got[0][0])) < 1e-6
+        api['e2e_list_api'] = {'value': m / dt, 'unit': 'queries/s', 'batch': m, 'ms': dt * 1e3,
+                               'what': 'Predictor.predict_batch(nested Python lists) -> nested lists (the reference\'s '
+                                       'types; list -> uint8 conversion on the host dominates), wall clock'}
 
     if rank == 0:
         peaks = load_peaks()
@@ -416,44 +558,63 @@ def main():
         flops_per_launch = flops_per_query_local * n
         ms_launch = ms / args.steps
         achieved = flops_per_launch / (ms_launch * 1e-3) / 1e12
-        peak = float(peaks.get('bf16_tflops_sustained', FALLBACK_PEAKS['bf16_tflops_sustained']))
-        traffic = None
+        peak_sus = float(peaks.get('bf16_tflops_sustained', FALLBACK_PEAKS['bf16_tflops_sustained']))
+        peak_burst = float(peaks.get('bf16_tflops', FALLBACK_PEAKS['bf16_tflops']))
+        # a timed region of a few ms on a cool chip is the burst regime; seconds at the power cap the sustained one
+        capped = bool(clocks and 'sw_power_cap' in (clocks.get('reasons') or []))
+        use_burst = ms < 1000.0 and not capped
+        peak = peak_burst if use_burst else peak_sus
+        traffic, traffic_source = None, None
         summ = os.path.join(ROOT, 'profiles', 'ncu_summary.json')
-        if os.path.exists(summ):
+        if os.path.exists(summ) and world == 1:
             try:
-                traffic = json.load(open(summ)).get(args.workload, {}).get('fused_dram_bytes_per_launch') if world == 1 else None
+                ent = json.load(open(summ)).get(args.workload, {})
+                traffic = ent.get('fused_dram_bytes_per_launch')
+                traffic_source = 'ncu capture {} (not measured in this run)'.format(ent.get('source', 'profiles/'))
             except Exception:
                 traffic = None
+        if do_reduce:
+            par = 'trial-per-gpu x{} + {}'.format(world, {
+                'peer': 'peer-memory reduce-scatter kernel, one native call per step (rfk_peer_ensemble_step)',
+                'gather': 'epilogue stores into the root over NVLink + sum',
+                'nccl': 'torch.distributed NCCL reduce'}[args.reduce])
+        elif wl.get('shard') == 'rows':
+            par = 'rows sharded x{}'.format(world)
+        else:
+            par = 'replicas x{}'.format(world) if world > 1 else 'single gpu, fused ensemble'
         line = {
             'metric': 'ensemble_queries_per_sec', 'value': value, 'unit': 'queries/s', 'n_gpus': world,
-            'steps': args.steps, 'warmup': max(args.warmup, 3), 'ms_per_step': ms / args.steps,
+            'steps': args.steps, 'warmup': warm, 'ms_per_step': ms / args.steps, 'ms_median_step': ms_median_step,
             'higher_is_better': True, 'scaling': wl['scaling'], 'vs_baseline': None, 'dtype': args.compute,
             'data': 'synthetic',
             'config': {'workload': wl['name'], 'trials': W, 'batch': n, 'd': d, 'hidden_units': wl['hidden'],
-                       'hidden_layers': wl['layers'], 'classes': C,
-                       'parallelism': ('trial-per-gpu x{} + {}'.format(world, ('epilogue stores into the root over NVLink + sum' if args.reduce == 'gather' else
-                                                                        'peer-memory reduce-scatter kernel') if
-                                                                       reducer is not None else 'nccl reduce')
-                                       if do_reduce else
-                                       ('rows sharded x{}'.format(world) if wl.get('shard') == 'rows' else
-                                        ('replicas x{}'.format(world) if world > 1 else 'single gpu, fused ensemble'))),
+                       'hidden_layers': wl['layers'], 'classes': C, 'parallelism': par,
                        'l2': 'rotating over {} distinct resident batches ({} MB > L2)'.format(
                            len(xs), len(xs) * n * d // (1 << 20))},
             'clocks': clocks,
             'latency': latency,
             'e2e': e2e,
-            'gpu_launches': args.steps * ((len(params[0]['kernels']) + 1) if wl.get('shard') == 'rows' else
-                                          ((1 if ens is not None else 0) + (2 if reducer is not None else 0))),
+            'gpu_launches': int(launches),
+            'gpu_launches_source': 'rfk_launch_count() before/after the timed region on rank 0',
             'roofline': {'bound': 'tensor', 'achieved': achieved, 'peak': peak, 'unit': 'TFLOP/s',
-                         'frac': achieved / peak, 'traffic': traffic,
+                         'frac': achieved / peak, 'frac_burst': achieved / peak_burst,
+                         'frac_sustained': achieved / peak_sus,
+                         'peak_choice': 'burst' if use_burst else 'sustained',
+                         'traffic': traffic, 'traffic_source': traffic_source,
                          'kernel': ('gemm_bias_act_kernel x4 + decode (whole step; duration = timed region / steps)'
                                     if wl.get('shard') == 'rows' else
                                     'fused_ensemble_kernel (one launch per step; duration = timed region / steps)'),
-                         'peak_source': peaks['_source'] + ', bf16_tflops_sustained (same rate for fp16)',
+                         'peak_source': peaks['_source'] + ' (bf16 rates; same tensor rate for fp16)',
                          'flops_per_launch': flops_per_launch,
                          'hbm_gbs_algorithmic': n * (d + 4 * C) / (ms_launch * 1e-3) / 1e9},
         }
-        if not args.no_cpu_baseline:
+        line.update(api)
+        if parity is not None:
+            line['parity_vs_single_gpu'] = parity
+            if not parity <= 1e-6:
+                print(json.dumps(line), flush=True)
+                raise SystemExit('N = {} result differs from the single-GPU ensemble by {}'.format(world, parity))
+        if not args.no_cpu_baseline and world == 1:
             cores = os.cpu_count() or 1
             sample = min(n, 4096)
             rate, times = cpu_oracle_rate(params, batches[0], sample, 2, cores)
