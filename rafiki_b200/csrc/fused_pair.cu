@@ -1,0 +1,699 @@
+// Kernels 1+2 for large batches on CTA PAIRS: the trial's weights stay in shared memory.
+//
+// Same arithmetic and the same reference code replaced as fused_trial.cu (InferenceWorker predict,
+// rafiki/worker/inference.py:53 -> TfFeedForward.predict, TfFeedForward.py:89-97,141-157); what
+// changes is where the bytes travel.  fused_trial.cu streams the first-layer weights (200 KB per
+// 128-query tile and trial) from L2 into every SM again for every tile: at batch 65536 x 8 trials
+// that is 1.2 GB through L2 per launch, and the kernel runs at the chip's L2 -> SM throughput
+// (about 42 B/clk per SM measured: 300 KB per item / 7100 cycles), not at the tensor pipe's.
+// Here two CTAs of a cluster work as one 256-query tile (tcgen05 cta_group::2, M = 256): each
+// CTA keeps HALF of the hidden units' weight rows (W1: 104 KB for d 784, W2: 16 KB, W3: 2 KB) in
+// shared memory for as long as the pair stays on one trial, and the only per-tile traffic is the
+// uint8 tile itself.  The loop order is therefore trial-outer: a pair takes a contiguous range of
+// (trial, 256-query tile) items in trial-major order, reloads the weights when the trial changes
+// (at most once or twice per launch), and writes per-trial probabilities; the cross-trial mean is
+// kernel 3 (ensemble.cu) over those, in float64 in trial order with one rounding -- the same sum
+// the single-CTA kernel keeps in registers.
+//
+// Roles per CTA (640 threads, as in fused_trial.cu): epilogue x 8 warps, converters x 8 (uint8 ->
+// fp16 into tensor memory), loader (TMA of raw tiles; bulk copies of the weights at a trial
+// change), layer-1 MMA issuer and layers-2/3 MMA issuer (LEADER CTA only: one thread issues for
+// both CTAs), and a warp that forwards "weights landed" to the leader.  Hand-offs that cross the
+// pair (operands ready, accumulator drained) are arrivals on the leader's mbarriers through the
+// cluster window; completions come back as tcgen05.commit multicast to both CTAs.  No load here is
+// a multicast load: every CTA fetches its own bytes.
+#include <stdlib.h>
+
+#include "fused_common.cuh"
+#include "pack.cuh"
+#include "rfk_internal.cuh"
+#include "sm100.cuh"
+#include "tmap.cuh"
+
+namespace {
+
+using namespace sm100;
+using namespace fusedk;
+
+constexpr int TILE_M = 128;          // rows per CTA; a pair covers 256
+constexpr int ATOM_K = 64;
+constexpr int KB = 128;              // K elements per raw stage (one TMA box)
+constexpr int A_STAGES = 5;          // A operand ring in tensor memory: stages of ONE 64-wide K atom
+constexpr int A_COLS = ATOM_K / 2;   // 32 columns per stage
+constexpr int MAX_RAW_STAGES = 6;
+constexpr int MIN_RAW_STAGES = 3;
+constexpr int HMAX = 128;
+constexpr int HHALF = HMAX / 2;      // weight rows (hidden units) per CTA
+constexpr int CPAD = 16;
+constexpr int W1_ATOM = HHALF * 128;              // 8 KB: one 64-wide K atom of this CTA's half of W1
+constexpr int W2_BYTES = 2 * HHALF * 128;         // 16 KB
+constexpr int W3_ATOM = (CPAD / 2) * 128;         // 1 KB: 8 class rows per CTA
+constexpr int W3_BYTES = 2 * W3_ATOM;
+constexpr int RAW_STAGE = TILE_M * KB;            // 16 KB of uint8
+constexpr int BIAS_FLOATS = HMAX + HMAX + CPAD;   // b1 | b2 | b3
+constexpr int BIAS_BYTES = BIAS_FLOATS * 4;
+constexpr int OUT_BYTES = TILE_M * CPAD * 4;
+constexpr int SMEM_MAX = 227 * 1024;
+
+constexpr int kEpiWarps = 8, kConvWarps = 8;
+constexpr int kThreads = (kEpiWarps + kConvWarps + 4) * 32;   // 640
+// role indices (see the mapping from physical warps in the kernel)
+constexpr int WARP_LOAD = kEpiWarps + kConvWarps, WARP_MMA = WARP_LOAD + 1, WARP_FWD = WARP_LOAD + 2,
+              WARP_TAIL = WARP_LOAD + 3;
+constexpr int kRegsLaunch = 96;
+constexpr int kRegsEpi = 136, kRegsConv = 72, kRegsLight = 56;
+// setmaxnreg.inc only hands out what the CTA's own warps have given back (the launch allocation)
+static_assert(kEpiWarps * kRegsEpi + kConvWarps * kRegsConv + 4 * kRegsLight <= (kEpiWarps + kConvWarps + 4) * kRegsLaunch,
+              "setmaxnreg budget exceeds the launch allocation");
+constexpr int BAR_SOFTMAX = 1;
+
+constexpr int TMEM_COLS = 512;
+constexpr int COL_ACC1 = 0;     // 2 x 128: layer-1 accumulators (layer 2 accumulates into the drained buffer)
+constexpr int COL_A = 256;      // A ring: A_STAGES x 32 columns
+constexpr int COL_HID = 416;    // hidden activations (16-bit pairs): 64 columns
+constexpr int COL_ACC3 = 480;
+static_assert(COL_A + A_STAGES * A_COLS <= COL_HID && COL_HID + HMAX / 2 <= COL_ACC3 && COL_ACC3 + CPAD <= TMEM_COLS,
+              "tensor memory map");
+
+struct PairTrial {
+  const uint8_t* w1;    // [n_atoms][h1_pad rows][128 B] swizzled (the single-CTA kernel's image)
+  const uint8_t* w2;    // [h1_pad / 64][h2_pad rows][128 B]
+  const uint8_t* w3;    // [hl_pad / 64][16 rows][128 B]
+  const float* bias;    // [BIAS_FLOATS]
+  int h1_pad, h2_pad, n_hidden, pad_;
+};
+
+struct PairParams {
+  PairTrial trial[RFK_MAX_TRIALS];
+  float* out;                 // trial t writes out + t * trial_stride
+  long long trial_stride;     // elements between the outputs of consecutive trials (0: a single trial)
+  long long n;
+  double divisor;             // the stored value is float(p / divisor)
+  int d, n_kb, n_atoms, w, n_classes, n_pt, raw_stages;
+  int items_q, items_r;       // items per pair: pair p takes items_q (+ 1 if p < items_r), in order
+  int off_w2, off_w3, off_raw, off_bias, off_out, off_bar;
+  int debug;            // development (RFK_PAIR_DEBUG): 4 = skip the layer-1 MMAs
+  long long* trace;     // development (RFK_PAIR_TRACE): event timestamps of pair 0, [2 CTAs][5 roles][kTraceLen]
+};
+constexpr int kTraceLen = 1024;
+#define PTRACE(role, tag)                                                                              \
+  do {                                                                                               \
+    if (kTrace && P.trace != nullptr && blockIdx.x < 2 && lane == 0 && trace_n < kTraceLen) {          \
+      P.trace[((int)blockIdx.x * 5 + (role)) * kTraceLen + trace_n] = (clock64() << 4) | (long long)(tag); \
+      ++trace_n;                                                                                     \
+    }                                                                                                \
+  } while (0)
+
+struct PBars {
+  uint64_t raw_full[MAX_RAW_STAGES], raw_empty[MAX_RAW_STAGES];   // own CTA
+  uint64_t a_full[A_STAGES];      // leader: 2 x 4 converter warps (the group that owns the atom's 64 bytes of every row)
+  uint64_t a_free[A_STAGES];      // both: the MMAs that read the stage are complete (multicast commit)
+  uint64_t acc1_full[2];          // both (multicast commit)
+  uint64_t acc1_empty[2];         // leader: 2 x 8 epilogue warps
+  uint64_t hid_ready;             // leader: 2 x 8 epilogue warps
+  uint64_t acc2_full, acc3_full;  // both (multicast commit)
+  uint64_t w_full;                // own CTA: this trial's weights landed (transaction bytes)
+  uint64_t w_free;                // own CTA: 8 epilogue warps are done with the previous trial's weights
+  uint64_t w_ready;               // leader: both CTAs' weights landed
+};
+constexpr int TAIL_BYTES = 10 * 1024;   // bias + output staging + barriers + TMEM slot, after the raw ring
+static_assert(((BIAS_BYTES + 15) / 16 * 16) + OUT_BYTES + (int)sizeof(PBars) + 16 <= TAIL_BYTES, "tail region");
+
+// The items of a pair in order, without a division in the kernel (a 64-bit division is a call, and
+// values that come back from a call are no longer warp-uniform for the compiler: the MMA issue then
+// falls off the uniform datapath).
+struct ItemIter {
+  int t, pt;
+  __device__ __forceinline__ void init(int first, int n_pt) {
+    t = 0;
+    pt = first;
+    while (pt >= n_pt) {
+      pt -= n_pt;
+      ++t;
+    }
+  }
+  __device__ __forceinline__ void next(int n_pt) {
+    if (++pt == n_pt) {
+      pt = 0;
+      ++t;
+    }
+  }
+};
+
+// leader-side arrival through the cluster window: one per warp (see warp_arrive in fused_common.cuh)
+__device__ __forceinline__ void warp_arrive_leader(uint32_t leader_bar_addr) {
+  __syncwarp();
+  if ((threadIdx.x & 31) == 0) mbar_arrive_cluster(leader_bar_addr);
+}
+
+// plain bulk copy, no arrival (the caller has posted the transaction bytes of the whole group)
+__device__ __forceinline__ void bulk_g2s_elect(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {
+  asm volatile(
+      "{\n\t.reg .pred q;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
+      "@q cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n\t}" ::"r"(
+          smem_u32(smem_dst)),
+      "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx_elect(uint64_t* bar, uint32_t bytes) {
+  asm volatile(
+      "{\n\t.reg .pred q;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
+      "@q mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n\t}" ::"r"(smem_u32(bar)), "r"(bytes)
+      : "memory");
+}
+
+// kTrace: development build with event timestamps (a lane-0 region after every hand-off makes the
+// issuing loops divergent for the compiler, so the production instantiation must not contain it)
+template <bool kF16, bool kTrace>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ CUtensorMap x_map) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
+  PBars* bars = reinterpret_cast<PBars*>(smem + P.off_bar);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + P.off_bar + sizeof(PBars));
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);   // warp-uniform for the compiler
+  const int lane = threadIdx.x & 31;
+  int trace_n = 0;
+  (void)trace_n;
+  const uint32_t rank = (uint32_t)blockIdx.x & 1u;      // == %cluster_ctarank for a cluster of 2 along x; 0 = leader
+  const bool leader = rank == 0;
+  if ((smem_u32(smem) & 1023u) != 0u || cluster_ctarank() != rank) {
+    if (threadIdx.x == 0) printf("rafiki_b200: pair kernel: misaligned shared memory or unexpected cluster rank\n");
+    __trap();
+  }
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < MAX_RAW_STAGES; ++s) {
+      mbar_init(&bars->raw_full[s], 1);
+      mbar_init(&bars->raw_empty[s], kConvWarps);
+    }
+    for (int s = 0; s < A_STAGES; ++s) {
+      mbar_init(&bars->a_full[s], kConvWarps);       // 4 warps of the owning group x 2 CTAs
+      mbar_init(&bars->a_free[s], 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&bars->acc1_full[b], 1);
+      mbar_init(&bars->acc1_empty[b], 2 * kEpiWarps);
+    }
+    mbar_init(&bars->hid_ready, 2 * kEpiWarps);
+    mbar_init(&bars->acc2_full, 1);
+    mbar_init(&bars->acc3_full, 1);
+    mbar_init(&bars->w_full, 1);
+    mbar_init(&bars->w_free, kEpiWarps);
+    mbar_init(&bars->w_ready, 2);
+    fence_mbar_init();
+  }
+  if (warp == WARP_LOAD && lane == 0) tma_prefetch_desc(&x_map);
+  if (warp == WARP_MMA) tmem_alloc_pair<TMEM_COLS>(tmem_slot);
+  tc_fence_before_sync();
+  cluster_sync_all();            // barriers of BOTH CTAs are initialised before anyone signals across the pair
+  tc_fence_after_sync();
+  if (*tmem_slot != 0u) {
+    if (threadIdx.x == 0) printf("rafiki_b200: unexpected TMEM base %u\n", *tmem_slot);
+    __trap();
+  }
+  constexpr uint32_t tmem_base = 0u;
+  const uint32_t smem_base = smem_u32(smem);
+  const int n_kb = P.n_kb;
+
+  // ---- this pair's items: a contiguous range of (trial, pair tile) in trial-major order
+  const int pair = (int)blockIdx.x >> 1;
+  const int i_lo = pair * P.items_q + (pair < P.items_r ? pair : P.items_r);
+  const int n_items = P.items_q + (pair < P.items_r ? 1 : 0);
+  // leader's barriers as seen through the cluster window
+  const uint32_t l_a_full0 = map_to_cta(smem_u32(&bars->a_full[0]), 0);
+  const uint32_t l_acc1_empty0 = map_to_cta(smem_u32(&bars->acc1_empty[0]), 0);
+  const uint32_t l_hid_ready = map_to_cta(smem_u32(&bars->hid_ready), 0);
+  const uint32_t l_w_ready = map_to_cta(smem_u32(&bars->w_ready), 0);
+
+  if (warp < kEpiWarps) {
+    // =============================================================== epilogue warps (own 128 rows)
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kRegsEpi));
+    const int quarter = warp & 3;
+    const int half = warp >> 2;                                // 0: hidden columns 0-63 + softmax; 1: columns 64-127
+    const int row = quarter * 32 + lane;
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(quarter * 32) << 16);
+    const uint32_t hid_row_addr = lane_addr + COL_HID;
+    const float* bias = reinterpret_cast<const float*>(smem + P.off_bias);
+    uint32_t v3[16];
+    bool have_prev = false;
+    int prev_t = 0, prev_pt = 0;
+    auto finish_prev = [&]() {
+      // logits (v3) + bias -> softmax -> this trial's probabilities, staged and stored with 16-byte stores
+      if (half == 0) {
+        float z[CPAD];
+        const float inv = softmax16(v3, bias + 2 * HMAX, P.n_classes, z);
+        const int C = P.n_classes;
+        const float* stage = reinterpret_cast<const float*>(smem + P.off_out);
+        const uint32_t dst = smem_base + (uint32_t)P.off_out + (uint32_t)(row * C) * 4u;
+        // a lone trial of a larger ensemble stores float(p / total) rounded once from float64 (what the
+        // single-CTA kernel stores); per-trial outputs for kernel 3 are stored as they are -- a float64
+        // division costs thousands of cycles per tile and must stay off that path
+        if (P.divisor == 1.0) {
+#pragma unroll
+          for (int j = 0; j < CPAD; ++j) sts_f32_if(dst + 4u * j, z[j] * inv, j < C);
+        } else {
+#pragma unroll
+          for (int j = 0; j < CPAD; ++j) sts_f32_if(dst + 4u * j, (float)((double)(z[j] * inv) / P.divisor), j < C);
+        }
+        named_bar_sync(BAR_SOFTMAX, 128);
+        {
+          const long long first = (long long)prev_pt * (2 * TILE_M) + (long long)rank * TILE_M;
+          long long rows = P.n - first;
+          rows = rows < 0 ? 0 : (rows < TILE_M ? rows : TILE_M);
+          store_tile_probs(P.out + (long long)prev_t * P.trial_stride + first * C, stage, (int)rows * C, row);
+        }
+        named_bar_sync(BAR_SOFTMAX, 128);
+      }
+    };
+    auto fetch_prev_logits = [&](uint32_t parity) {
+      // both halves wait: the hidden tile may not be overwritten before the layer-3 MMAs have read it
+      mbar_wait(&bars->acc3_full, parity);
+      tc_fence_after_sync();
+      if (half == 0) {
+        tmem_ld16(lane_addr + COL_ACC3, v3);
+        tmem_ld_wait();
+      }
+    };
+    int epoch = 0, cur_t = -1;
+    uint32_t acc2_phase = 0;
+    ItemIter it;
+    it.init(i_lo, P.n_pt);
+    for (int item = 0; item < n_items; ++item, it.next(P.n_pt)) {
+      const PairTrial& T = P.trial[it.t];
+      const int buf = item & 1;
+      const uint32_t par2 = (uint32_t)((item >> 1) & 1);
+      if (it.t != cur_t) {
+        // a new trial: finish the last item of the old one (its softmax reads the old b3), hand the weight
+        // buffers back to the loader, wait for the new trial's parameters
+        if (have_prev) {
+          fetch_prev_logits((uint32_t)((item - 1) & 1));
+          tc_fence_before_sync();
+          finish_prev();
+          have_prev = false;
+        }
+        if (epoch > 0) warp_arrive(&bars->w_free);
+        mbar_wait(&bars->w_full, (uint32_t)(epoch & 1));
+        ++epoch;
+        cur_t = it.t;
+      }
+      // ---- layer 1: acc1[buf] -> hidden
+      mbar_wait(&bars->acc1_full[buf], par2);
+      if (warp == 0) PTRACE(3, 1);
+      if (have_prev) fetch_prev_logits((uint32_t)((item - 1) & 1));
+      if (warp == 0) PTRACE(3, 5);
+      tc_fence_after_sync();
+      {
+        const int split = T.h1_pad < 64 ? T.h1_pad : 64;
+        epilogue_hidden<kF16>(lane_addr + COL_ACC1 + buf * HMAX, half ? split : 0, half ? T.h1_pad : split, bias,
+                              kF16 ? kSubnormalScale : 1.0f, hid_row_addr);
+      }
+      tc_fence_before_sync();
+      warp_arrive_leader(l_hid_ready);
+      if (T.n_hidden != 2) warp_arrive_leader(l_acc1_empty0 + 8u * buf);
+      if (warp == 0) PTRACE(3, 2);
+      if (have_prev) finish_prev();
+      if (warp == 0) PTRACE(3, 6);
+      if (T.n_hidden == 2) {
+        mbar_wait(&bars->acc2_full, acc2_phase);
+        if (warp == 0) PTRACE(3, 3);
+        acc2_phase ^= 1u;
+        tc_fence_after_sync();
+        const int split = T.h2_pad < 64 ? T.h2_pad : 64;
+        epilogue_hidden<kF16>(lane_addr + COL_ACC1 + buf * HMAX, half ? split : 0, half ? T.h2_pad : split, bias + HMAX,
+                              1.0f, hid_row_addr);
+        tc_fence_before_sync();
+        warp_arrive_leader(l_hid_ready);
+        warp_arrive_leader(l_acc1_empty0 + 8u * buf);
+        if (warp == 0) PTRACE(3, 4);
+      }
+      have_prev = true;
+      prev_t = it.t;
+      prev_pt = it.pt;
+    }
+    if (have_prev) {
+      fetch_prev_logits((uint32_t)((n_items - 1) & 1));
+      tc_fence_before_sync();
+      finish_prev();
+    }
+  } else if (warp < kEpiWarps + kConvWarps) {
+    // =============================================================== converter warps (own 128 rows)
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsConv));
+    const int quarter = warp & 3;
+    const int khalf = (warp - kEpiWarps) >> 2;
+    const int row = quarter * 32 + lane;
+    const uint32_t raw_row = smem_base + (uint32_t)P.off_raw + (uint32_t)row * 128u;
+    const uint32_t sw = (uint32_t)(row & 7);
+    uint32_t raw_chunk[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) raw_chunk[j] = raw_row + ((((uint32_t)(4 * khalf + j)) ^ sw) << 4);
+    const uint32_t a_dst0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + COL_A;
+    int rstage = 0;
+    uint32_t rphase = 0;
+    // A warp owns bytes [64 khalf, 64 khalf + 64) of its rows in every 128-byte raw stage, i.e. the K atom
+    // 2 kb + khalf of the item: one A stage (32 columns) of its own, handed to the issuer on its own barrier,
+    // so the ring turns over in 64-wide steps while a thread's work per raw stage stays the same.
+    for (int item = 0; item < n_items; ++item) {
+      for (int kb = 0; kb < n_kb; ++kb) {
+        const int atom = 2 * kb + khalf;
+        const bool have = atom < P.n_atoms;                 // the ragged end of the row may leave this group nothing
+        int live = (P.d - atom * ATOM_K + 15) >> 4;        // 16-byte chunks the MMAs will read
+        live = live < 0 ? 0 : (live > 4 ? 4 : live);
+        mbar_wait(&bars->raw_full[rstage], rphase);
+        if (warp == kEpiWarps) PTRACE(0, 1);
+        const uint32_t rsrc = (uint32_t)rstage * RAW_STAGE;
+        uint32_t p[32];
+#pragma unroll
+        for (int h2 = 0; h2 < 2; ++h2) {
+          if (live > 2 * h2) {
+            const uint4 r0 = lds_u4(raw_chunk[2 * h2] + rsrc), r1 = lds_u4(raw_chunk[2 * h2 + 1] + rsrc);
+            uint32_t* q = p + 16 * h2;
+            q[0] = u8x2_to_op<kF16>(r0.x, 0);  q[1] = u8x2_to_op<kF16>(r0.x, 2);
+            q[2] = u8x2_to_op<kF16>(r0.y, 0);  q[3] = u8x2_to_op<kF16>(r0.y, 2);
+            q[4] = u8x2_to_op<kF16>(r0.z, 0);  q[5] = u8x2_to_op<kF16>(r0.z, 2);
+            q[6] = u8x2_to_op<kF16>(r0.w, 0);  q[7] = u8x2_to_op<kF16>(r0.w, 2);
+            q[8] = u8x2_to_op<kF16>(r1.x, 0);  q[9] = u8x2_to_op<kF16>(r1.x, 2);
+            q[10] = u8x2_to_op<kF16>(r1.y, 0); q[11] = u8x2_to_op<kF16>(r1.y, 2);
+            q[12] = u8x2_to_op<kF16>(r1.z, 0); q[13] = u8x2_to_op<kF16>(r1.z, 2);
+            q[14] = u8x2_to_op<kF16>(r1.w, 0); q[15] = u8x2_to_op<kF16>(r1.w, 2);
+          }
+        }
+        warp_arrive(&bars->raw_empty[rstage]);
+        if (have) {
+          const int ga = item * P.n_atoms + atom;          // global atom counter of this pair
+          const int as = ga % A_STAGES;
+          if (ga >= A_STAGES) mbar_wait(&bars->a_free[as], (uint32_t)(((ga / A_STAGES) - 1) & 1));
+          if (warp == kEpiWarps) PTRACE(0, 2);
+          tc_fence_after_sync();
+          const uint32_t dst = a_dst0 + (uint32_t)as * A_COLS;
+#pragma unroll
+          for (int h2 = 0; h2 < 2; ++h2)
+            if (live > 2 * h2) tmem_st16(dst + 16u * h2, *reinterpret_cast<const uint32_t(*)[16]>(p + 16 * h2));
+          tmem_st_wait();
+          tc_fence_before_sync();
+          warp_arrive_leader(l_a_full0 + 8u * as);
+          if (warp == kEpiWarps) PTRACE(0, 3);
+        }
+        if (++rstage == P.raw_stages) { rstage = 0; rphase ^= 1u; }
+      }
+    }
+  } else {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsLight));
+  }
+  if (warp == WARP_LOAD) {
+    // =============================================================== loader (own CTA's shared memory)
+    // At a trial change: this CTA's half of W1 / W2 / W3 and the biases, one transaction group on
+    // w_full, once the epilogue warps have released the buffers.  Per raw stage: the uint8 tile of
+    // this CTA's 128 rows, 128 columns.
+    int rstage = 0, epoch = 0, cur_t = -1;
+    uint32_t rphase = 0;
+    ItemIter it;
+    it.init(i_lo, P.n_pt);
+    for (int item = 0; item < n_items; ++item, it.next(P.n_pt)) {
+      if (it.t != cur_t) {
+        const PairTrial& T = P.trial[it.t];
+        if (epoch > 0) mbar_wait(&bars->w_free, (uint32_t)((epoch - 1) & 1));
+        const uint32_t w1_half = (uint32_t)(T.h1_pad >> 1) * 128u;               // bytes of one atom's half
+        const int hl_pad = T.n_hidden == 2 ? T.h2_pad : T.h1_pad;
+        const int atoms2 = T.n_hidden == 2 ? (T.h1_pad + 63) / 64 : 0, atoms3 = (hl_pad + 63) / 64;
+        const uint32_t w2_half = (uint32_t)(T.h2_pad >> 1) * 128u;
+        const uint32_t total = (uint32_t)P.n_atoms * w1_half + (uint32_t)atoms2 * w2_half + (uint32_t)atoms3 * W3_ATOM +
+                               BIAS_BYTES;
+        mbar_expect_tx_elect(&bars->w_full, total);
+        for (int a = 0; a < P.n_atoms; ++a)
+          bulk_g2s_elect(smem + a * W1_ATOM, T.w1 + (size_t)a * 2 * w1_half + (size_t)rank * w1_half, w1_half, &bars->w_full);
+        for (int a = 0; a < atoms2; ++a)
+          bulk_g2s_elect(smem + P.off_w2 + a * (HHALF * 128), T.w2 + (size_t)a * 2 * w2_half + (size_t)rank * w2_half,
+                         w2_half, &bars->w_full);
+        for (int a = 0; a < atoms3; ++a)
+          bulk_g2s_elect(smem + P.off_w3 + a * W3_ATOM, T.w3 + (size_t)a * 2 * W3_ATOM + (size_t)rank * W3_ATOM, W3_ATOM,
+                         &bars->w_full);
+        bulk_g2s_elect(smem + P.off_bias, T.bias, BIAS_BYTES, &bars->w_full);
+        ++epoch;
+        cur_t = it.t;
+      }
+      const int row0 = it.pt * (2 * TILE_M) + (int)rank * TILE_M;
+      for (int kb = 0; kb < n_kb; ++kb) {
+        mbar_wait(&bars->raw_empty[rstage], rphase ^ 1u);
+        PTRACE(1, 1);
+        tma_load_2d_expect_elect(smem + P.off_raw + rstage * RAW_STAGE, &x_map, kb * KB, row0, RAW_STAGE,
+                                 &bars->raw_full[rstage]);
+        if (++rstage == P.raw_stages) { rstage = 0; rphase ^= 1u; }
+      }
+    }
+  } else if (warp == WARP_FWD) {
+    // =============================================================== "weights landed" -> the leader
+    int epoch = 0, cur_t = -1;
+    ItemIter it;
+    it.init(i_lo, P.n_pt);
+    for (int item = 0; item < n_items; ++item, it.next(P.n_pt)) {
+      if (it.t != cur_t) {
+        mbar_wait(&bars->w_full, (uint32_t)(epoch & 1));
+        warp_arrive_leader(l_w_ready);
+        ++epoch;
+        cur_t = it.t;
+      }
+    }
+  } else if (warp == WARP_MMA && leader) {
+    // =============================================================== layer-1 MMA issuer (leader CTA, for the pair)
+    // A: tensor memory of each CTA (its own 128 rows); B: each CTA's half of W1, resident; D: tensor
+    // memory of each CTA.  One commit per atom hands the A stage back to the converters of both CTAs.
+    const uint32_t w1_lo0 = desc_lo_sw128(smem_base);
+    int gs = 0, as = 0, epoch = 0, cur_t = -1;
+    uint32_t aphase = 0;
+    ItemIter it;
+    it.init(i_lo, P.n_pt);
+    for (int item = 0; item < n_items; ++item, it.next(P.n_pt)) {
+      const PairTrial& T = P.trial[it.t];
+      if (it.t != cur_t) {
+        mbar_wait(&bars->w_ready, (uint32_t)(epoch & 1));
+        ++epoch;
+        cur_t = it.t;
+      }
+      const int buf = item & 1;
+      const uint32_t idesc1 = idesc_16bit_f32(kF16, 2 * TILE_M, T.h1_pad);
+      const uint32_t d_tmem = tmem_base + COL_ACC1 + buf * HMAX;
+      mbar_wait(&bars->acc1_empty[buf], (uint32_t)(((item >> 1) & 1) ^ 1));
+      PTRACE(2, 4);
+      for (int atom = 0; atom < P.n_atoms; ++atom, ++gs) {
+        mbar_wait(&bars->a_full[as], aphase);
+        PTRACE(2, 1);
+        tc_fence_after_sync();
+        const int k16 = (P.d - atom * ATOM_K) >> 4;
+        const uint32_t a = tmem_base + COL_A + (uint32_t)as * A_COLS;
+        const uint32_t b = w1_lo0 + (uint32_t)atom * (W1_ATOM >> 4);
+        if (!(P.debug & 4)) mma4_f16_ts_pair_elect(d_tmem, a, desc_from_lo(b), idesc1, atom != 0, k16 < 4 ? k16 : 4);
+        PTRACE(2, 2);
+        mma_commit_pair_elect(&bars->a_free[as]);
+        if (++as == A_STAGES) { as = 0; aphase ^= 1u; }
+      }
+      mma_commit_pair_elect(&bars->acc1_full[buf]);
+    }
+  } else if (warp == WARP_TAIL && leader) {
+    // =============================================================== layers 2 and 3 (leader CTA, for the pair)
+    const uint32_t w2_lo = desc_lo_sw128(smem_base + (uint32_t)P.off_w2), w3_lo = desc_lo_sw128(smem_base + (uint32_t)P.off_w3);
+    auto issue_small_layer = [&](uint32_t d_tmem, uint32_t b_lo, uint32_t b_atom, uint32_t idesc, int ksteps) {
+      for (int k0 = 0; k0 < ksteps; k0 += 4) {
+        const uint32_t a = tmem_base + COL_HID + (uint32_t)k0 * 8u;
+        const uint32_t b = b_lo + (uint32_t)(k0 >> 2) * b_atom;
+        mma4_f16_ts_pair_elect(d_tmem, a, desc_from_lo(b), idesc, k0 != 0, ksteps - k0 < 4 ? ksteps - k0 : 4);
+      }
+    };
+    int epoch = 0, cur_t = -1;
+    uint32_t hid_phase = 0;
+    ItemIter it;
+    it.init(i_lo, P.n_pt);
+    for (int item = 0; item < n_items; ++item, it.next(P.n_pt)) {
+      const PairTrial& T = P.trial[it.t];
+      if (it.t != cur_t) {
+        mbar_wait(&bars->w_ready, (uint32_t)(epoch & 1));
+        ++epoch;
+        cur_t = it.t;
+      }
+      const int buf = item & 1;
+      if (T.n_hidden == 2) {
+        mbar_wait(&bars->hid_ready, hid_phase);
+        PTRACE(4, 1);
+        hid_phase ^= 1u;
+        tc_fence_after_sync();
+        issue_small_layer(tmem_base + COL_ACC1 + (uint32_t)buf * HMAX, w2_lo, (HHALF * 128u) >> 4,
+                          idesc_16bit_f32(kF16, 2 * TILE_M, T.h2_pad), T.h1_pad >> 4);
+        mma_commit_pair_elect(&bars->acc2_full);
+        PTRACE(4, 2);
+      }
+      mbar_wait(&bars->hid_ready, hid_phase);
+      PTRACE(4, 3);
+      hid_phase ^= 1u;
+      tc_fence_after_sync();
+      const int hl_pad = T.n_hidden == 2 ? T.h2_pad : T.h1_pad;
+      issue_small_layer(tmem_base + COL_ACC3, w3_lo, (uint32_t)W3_ATOM >> 4, idesc_16bit_f32(kF16, 2 * TILE_M, CPAD), hl_pad >> 4);
+      mma_commit_pair_elect(&bars->acc3_full);
+      PTRACE(4, 4);
+    }
+  }
+  __syncwarp();
+  tc_fence_before_sync();
+  cluster_sync_all();            // neither CTA leaves (or frees tensor memory) while the other may still signal it
+  if (warp == WARP_MMA) tmem_dealloc_pair<TMEM_COLS>(tmem_base);
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------- host side
+namespace rfk {
+
+namespace {
+constexpr int kMinPairTiles = 37;     // below this the single-CTA kernel's finer tiles fill the GPU better
+
+struct PairLayout {
+  int off_w2, off_w3, off_raw, raw_stages, off_bias, off_out, off_bar, total;
+};
+bool pair_layout(int d, PairLayout* L) {
+  const int n_atoms = (d + ATOM_K - 1) / ATOM_K;
+  L->off_w2 = n_atoms * W1_ATOM;
+  L->off_w3 = L->off_w2 + W2_BYTES;
+  L->off_raw = L->off_w3 + W3_BYTES;
+  int stages = (SMEM_MAX - TAIL_BYTES - L->off_raw) / RAW_STAGE;
+  if (stages < MIN_RAW_STAGES) return false;
+  if (stages > MAX_RAW_STAGES) stages = MAX_RAW_STAGES;
+  L->raw_stages = stages;
+  L->off_bias = L->off_raw + stages * RAW_STAGE;
+  L->off_out = L->off_bias + (BIAS_BYTES + 15) / 16 * 16;
+  L->off_bar = L->off_out + OUT_BYTES;
+  L->total = L->off_bias + TAIL_BYTES;
+  return true;
+}
+}  // namespace
+
+// The pair kernel takes a batch when it is large enough to give every pair work and the trial's
+// half-weights plus a raw ring fit in shared memory.  The choice depends on n and d only, never on
+// the number of trials, so a trial alone and the same trial inside an ensemble run the same kernel.
+bool pair_applicable(int d, int64_t n) {
+  PairLayout L;
+  if (getenv("RFK_NO_PAIR") != nullptr) return false;
+  const int64_t n_pt = (n + 2 * TILE_M - 1) / (2 * TILE_M);
+  return n_pt >= kMinPairTiles && n_pt < (1ll << 22) && pair_layout(d, &L);
+}
+
+size_t pair_workspace_bytes(int w, int n_classes, int64_t n) {
+  return w > 1 ? (size_t)w * (size_t)n * (size_t)n_classes * sizeof(float) : 0;
+}
+
+int pair_forward(rfk_mlp* const* trials, int w, int total_trials, const uint8_t* x, int64_t n, float* out, void* ws,
+                 size_t ws_bytes, cudaStream_t st) {
+  RFK_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0, "fused forward: x must be 16-byte aligned");
+  const int d = trials[0]->d;
+  PairLayout L;
+  RFK_REQUIRE(pair_layout(d, &L), "pair kernel: d = %d does not fit in shared memory", d);
+  RFK_REQUIRE(w == 1 || (ws != nullptr && ws_bytes >= pair_workspace_bytes(w, trials[0]->n_classes, n)),
+              "pair kernel: workspace of %zu bytes needed", pair_workspace_bytes(w, trials[0]->n_classes, n));
+  CUtensorMap x_map;
+  {
+    const int rc = make_tmap_u8_2d(&x_map, x, (uint64_t)n, (uint64_t)d, (uint64_t)d, TILE_M, KB, true);
+    if (rc != RFK_OK) return rc;
+  }
+  PairParams P;
+  memset(&P, 0, sizeof(P));
+  for (int t = 0; t < w; ++t) {
+    FusedImages im;
+    RFK_REQUIRE(fused_images(trials[t], &im), "pair kernel: trial %d was not packed for the fused path", t);
+    P.trial[t].w1 = im.w1;
+    P.trial[t].w2 = im.w2;
+    P.trial[t].w3 = im.w3;
+    P.trial[t].bias = im.bias;
+    P.trial[t].h1_pad = im.h1_pad;
+    P.trial[t].h2_pad = im.h2_pad;
+    P.trial[t].n_hidden = im.n_hidden;
+  }
+  const int C = trials[0]->n_classes;
+  P.n = n;
+  P.d = d;
+  P.n_kb = (d + KB - 1) / KB;
+  P.n_atoms = (d + ATOM_K - 1) / ATOM_K;
+  P.w = w;
+  P.n_classes = C;
+  P.n_pt = (int)((n + 2 * TILE_M - 1) / (2 * TILE_M));
+  P.raw_stages = L.raw_stages;
+  P.off_w2 = L.off_w2;
+  P.off_w3 = L.off_w3;
+  P.off_raw = L.off_raw;
+  P.off_bias = L.off_bias;
+  P.off_out = L.off_out;
+  P.off_bar = L.off_bar;
+  if (w == 1) {
+    P.out = out;
+    P.trial_stride = 0;
+    P.divisor = (double)total_trials;
+  } else {
+    P.out = static_cast<float*>(ws);
+    P.trial_stride = (long long)n * C;
+    P.divisor = 1.0;
+  }
+  {
+    const char* dbg = getenv("RFK_PAIR_DEBUG");
+    P.debug = dbg ? atoi(dbg) : 0;
+  }
+  const bool f16 = trials[0]->dtype == RFK_F16;
+  const char* trace_path = getenv("RFK_PAIR_TRACE");
+  long long* dtrace = nullptr;
+  const size_t trace_elems = 2 * 5 * kTraceLen;
+  if (trace_path != nullptr && f16) {      // development aid: allocates and synchronises
+    RFK_CUDA_TRY(cudaMalloc(&dtrace, trace_elems * sizeof(long long)));
+    RFK_CUDA_TRY(cudaMemsetAsync(dtrace, 0, trace_elems * sizeof(long long), st));
+    P.trace = dtrace;
+  }
+  static bool attr_set = false;
+  if (!attr_set) {
+    RFK_CUDA_TRY(cudaFuncSetAttribute(fused_pair_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_MAX));
+    RFK_CUDA_TRY(cudaFuncSetAttribute(fused_pair_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_MAX));
+    RFK_CUDA_TRY(cudaFuncSetAttribute(fused_pair_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_MAX));
+    cudaFuncAttributes fa;
+    RFK_CUDA_TRY(cudaFuncGetAttributes(&fa, fused_pair_kernel<true, false>));
+    if (fa.numRegs * (kEpiWarps + kConvWarps + 4) < kEpiWarps * kRegsEpi + kConvWarps * kRegsConv + 4 * kRegsLight) {
+      set_error("pair kernel was compiled with %d registers per thread; its setmaxnreg budget needs %d", fa.numRegs,
+                kRegsLaunch);
+      return RFK_ERR_UNSUPPORTED;
+    }
+    attr_set = true;
+  }
+  const long long items = (long long)w * P.n_pt;
+  int pairs = num_sms() / 2;
+  if (items < pairs) pairs = (int)items;
+  P.items_q = (int)(items / pairs);
+  P.items_r = (int)(items % pairs);
+  if (f16 && dtrace != nullptr)
+    fused_pair_kernel<true, true><<<2 * pairs, kThreads, L.total, st>>>(P, x_map);
+  else if (f16)
+    fused_pair_kernel<true, false><<<2 * pairs, kThreads, L.total, st>>>(P, x_map);
+  else
+    fused_pair_kernel<false, false><<<2 * pairs, kThreads, L.total, st>>>(P, x_map);
+  RFK_LAUNCH_CHECK("fused_pair_kernel");
+  if (dtrace != nullptr) {
+    std::vector<long long> hall(trace_elems);
+    RFK_CUDA_TRY(cudaMemcpyAsync(hall.data(), dtrace, trace_elems * sizeof(long long), cudaMemcpyDeviceToHost, st));
+    RFK_CUDA_TRY(cudaStreamSynchronize(st));
+    cudaFree(dtrace);
+    FILE* f = fopen(trace_path, "w");
+    if (f) {
+      static const char* roles[5] = {"conv", "load", "mma", "epi", "tail"};
+      for (int c = 0; c < 2; ++c)
+        for (int r = 0; r < 5; ++r)
+          for (int i = 0; i < kTraceLen; ++i) {
+            const long long v = hall[(c * 5 + r) * kTraceLen + i];
+            if (v != 0) fprintf(f, "%d %s %d %lld %lld\n", c, roles[r], i, v >> 4, v & 15);
+          }
+      fclose(f);
+    }
+  }
+  if (w > 1) {
+    const float* ptrs[RFK_MAX_TRIALS];
+    for (int t = 0; t < w; ++t) ptrs[t] = static_cast<const float*>(ws) + (size_t)t * (size_t)n * C;
+    int rc = rfk_ensemble_mean(ptrs, w, n, C, out, st);
+    if (rc != RFK_OK) return rc;
+    if (total_trials != w) return scale_inplace(out, n * (int64_t)C, (double)total_trials / (double)w, st);
+  }
+  return RFK_OK;
+}
+
+}  // namespace rfk

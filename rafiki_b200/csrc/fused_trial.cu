@@ -58,10 +58,12 @@
 #include "rfk_internal.cuh"
 #include "sm100.cuh"
 #include "tmap.cuh"
+#include "fused_common.cuh"
 
 namespace {
 
 using namespace sm100;
+using namespace fusedk;
 
 constexpr int TILE_M = 128;
 constexpr int ATOM_K = 64;      // K elements of one 128-byte swizzle atom of 16-bit operands
@@ -155,122 +157,6 @@ struct Bars {
 };
 static_assert(sizeof(Bars) == NUM_BARS * 8, "barrier block size");
 
-// exact uint8 -> bf16: float(b) = as_float(0x4B000000 | b) - 2^23 has at most 8 significant
-// bits, so its upper 16 bits ARE the bf16 value (no rounding).
-__device__ __forceinline__ uint32_t u8x2_to_bf16x2(uint32_t word, int e0) {
-  const float f0 = __uint_as_float(__byte_perm(word, 0x4B000000u, 0x7440u | e0)) - 8388608.0f;
-  const float f1 = __uint_as_float(__byte_perm(word, 0x4B000000u, 0x7440u | (e0 + 1))) - 8388608.0f;
-  return __byte_perm(__float_as_uint(f0), __float_as_uint(f1), 0x7632u);
-}
-// exact uint8 -> fp16: 0x6400 | b is the half 1024 + b (ulp 1 in [1024, 2048)); subtract 1024.
-__device__ __forceinline__ uint32_t u8x2_to_f16x2(uint32_t word, int e0) {
-  const uint32_t biased = __byte_perm(word, 0x64646464u, 0x4040u | (uint32_t)e0 | ((uint32_t)(e0 + 1) << 8));
-  uint32_t r;
-  asm("sub.rn.f16x2 %0, %1, %2;" : "=r"(r) : "r"(biased), "r"(0x64006400u));
-  return r;
-}
-// uint8 -> fp16 SUBNORMAL: the 16-bit pattern 0x00bb is the half-precision value b * 2^-24 (no implicit
-// bit), so zero-extending the bytes IS the conversion -- one PRMT per pair and no arithmetic.  The
-// tensor core multiplies subnormal operands exactly; the layer-1 epilogue scales the fp32
-// accumulator back by 2^24 inside the FFMA that adds the bias (a power of two: bit-identical to
-// converting to b itself).
-__device__ __forceinline__ uint32_t u8x2_to_f16x2_subnormal(uint32_t word, int e0) {
-  return __byte_perm(word, 0u, 0x4040u | (uint32_t)e0 | ((uint32_t)(e0 + 1) << 8));
-}
-constexpr float kSubnormalScale = 16777216.0f;   // 2^24
-template <bool kF16>
-__device__ __forceinline__ uint32_t u8x2_to_op(uint32_t word, int e0) {
-  return kF16 ? u8x2_to_f16x2_subnormal(word, e0) : u8x2_to_bf16x2(word, e0);
-}
-
-// relu(lo), relu(hi) -> packed 16-bit operand pair (lo in the low half), one instruction;
-// fp16 saturates at 65504 instead of overflowing to infinity
-template <bool kF16>
-__device__ __forceinline__ uint32_t relu_pack_x2(float lo, float hi) {
-  uint32_t r;
-  if (kF16)
-    asm("cvt.rn.relu.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
-  else
-    asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
-  return r;
-}
-
-__device__ __forceinline__ uint4 lds_u4(uint32_t addr) {
-  uint4 r;
-  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(addr));
-  return r;
-}
-__device__ __forceinline__ void sts_u4(uint32_t addr, uint4 v) {
-  asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
-               : "memory");
-}
-
-// 16 accumulator columns of one row -> bias + ReLU -> 16-bit pairs -> 8 columns of the hidden
-// activations in tensor memory (element k of the row lives in the low/high half of column k/2)
-template <bool kF16>
-__device__ __forceinline__ void hidden_store16(const uint32_t (&v)[16], int c, const float* bias, float scale,
-                                               uint32_t hid_row_addr) {
-  const float4* b4 = reinterpret_cast<const float4*>(bias + c);
-  uint32_t p[8];
-#pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    const float4 bb = b4[j];
-    p[2 * j] = relu_pack_x2<kF16>(fmaf(__uint_as_float(v[4 * j + 0]), scale, bb.x),
-                                  fmaf(__uint_as_float(v[4 * j + 1]), scale, bb.y));
-    p[2 * j + 1] = relu_pack_x2<kF16>(fmaf(__uint_as_float(v[4 * j + 2]), scale, bb.z),
-                                      fmaf(__uint_as_float(v[4 * j + 3]), scale, bb.w));
-  }
-  tmem_st8(hid_row_addr + (uint32_t)(c >> 1), p);
-}
-
-// Columns [c_begin, c_end) of one TMEM accumulator row -> hidden activations (A operand of the
-// next layer, kept in tensor memory).  16 columns per step; the TMEM load of step s+1 is in flight
-// while step s is converted and stored (two statically named buffers: everything stays in registers;
-// four buffers were measured to spill under the 96-register launch bound).
-template <bool kF16>
-__device__ __forceinline__ void epilogue_hidden(uint32_t tmem_row_addr, int c_begin, int c_end, const float* bias,
-                                                float scale, uint32_t hid_row_addr) {
-  if (c_begin < c_end) {
-    uint32_t va[16], vb[16];
-    tmem_ld16(tmem_row_addr + (uint32_t)c_begin, va);
-    for (int c = c_begin; c < c_end; c += 32) {
-      tmem_ld_wait();
-      const bool more_b = c + 16 < c_end;
-      if (more_b) tmem_ld16(tmem_row_addr + (uint32_t)c + 16u, vb);
-      hidden_store16<kF16>(va, c, bias, scale, hid_row_addr);
-      if (more_b) {
-        tmem_ld_wait();
-        if (c + 32 < c_end) tmem_ld16(tmem_row_addr + (uint32_t)c + 32u, va);
-        hidden_store16<kF16>(vb, c + 16, bias, scale, hid_row_addr);
-      }
-    }
-  }
-  tmem_st_wait();
-}
-
-// Hardware named barriers (bar.sync / bar.arrive): producers arrive without blocking, the consumer
-// syncs; `threads` counts both sides and is a multiple of 32.  Every lane of a warp executes them.
-__device__ __forceinline__ void named_bar_arrive(int id, int threads) {
-  asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(threads) : "memory");
-}
-__device__ __forceinline__ void named_bar_sync(int id, int threads) {
-  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
-}
-
-// One arrival per warp instead of one per thread: 32 arrivals on one mbarrier serialise in the
-// shared-memory atomic unit (~1 lane per cycle).  __syncwarp orders the lanes' earlier writes
-// (and their proxy / tcgen05 fences) before the elected lane's release-arrive.
-__device__ __forceinline__ void warp_arrive(uint64_t* bar) {
-  __syncwarp();
-  if ((threadIdx.x & 31) == 0) mbar_arrive(bar);
-}
-__device__ __forceinline__ void warp_arrive2(uint64_t* bar_a, uint64_t* bar_b) {
-  __syncwarp();
-  if ((threadIdx.x & 31) == 0) {
-    mbar_arrive(bar_a);
-    mbar_arrive(bar_b);
-  }
-}
 
 // kProf (development, RFK_FUSED_PROF=1): the leader thread of each warp role accumulates the
 // cycles it spends blocked on each kind of barrier and adds them to P.prof at exit.
@@ -392,19 +278,7 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
       const float* pbias = reinterpret_cast<const float*>(smem + OFF_BIAS + prev_buf * BIAS_BYTES);
       if (half == 0) {
         float z[CPAD];
-        float mx = -INFINITY;
-#pragma unroll
-        for (int j = 0; j < CPAD; ++j) {
-          z[j] = __uint_as_float(v3[j]) + pbias[2 * HMAX + j];
-          if (j < P.n_classes) mx = fmaxf(mx, z[j]);
-        }
-        float sum = 0.f;
-#pragma unroll
-        for (int j = 0; j < CPAD; ++j) {
-          z[j] = j < P.n_classes ? __expf(z[j] - mx) : 0.f;
-          sum += z[j];
-        }
-        const float inv = 1.0f / sum;
+        const float inv = softmax16(v3, pbias + 2 * HMAX, P.n_classes, z);
         warp_arrive(&bars->bias_free[prev_buf]);
 #pragma unroll
         for (int j = 0; j < CPAD; ++j) acc[j] += (double)(z[j] * inv);
@@ -416,25 +290,17 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
           // 4-byte stores would waste most of every packet).
           const int C = P.n_classes;
           float* stage = reinterpret_cast<float*>(smem + OFF_OUT);
+          const uint32_t dst = smem_base + OFF_OUT + (uint32_t)(row * C) * 4u;
+          const double total = (double)(P.split ? 1 : P.total_trials);
 #pragma unroll
-          for (int j = 0; j < CPAD; ++j)
-            if (j < C) stage[row * C + j] = (float)(acc[j] / (double)(P.split ? 1 : P.total_trials));
+          for (int j = 0; j < CPAD; ++j) sts_f32_if(dst + 4u * j, (float)(acc[j] / total), j < C);
 #pragma unroll
           for (int j = 0; j < CPAD; ++j) acc[j] = 0.0;
           named_bar_sync(BAR_SOFTMAX, 128);                       // the four softmax warps
           {
             const long long first = (long long)prev_tile * TILE_M;
             const long long rows = P.n - first < TILE_M ? P.n - first : TILE_M;
-            const int valid = (int)rows * C;                        // floats of this tile that exist
-            float* o = P.out + (P.split ? (long long)t0 * P.n * C : 0ll) + first * C;
-            if ((reinterpret_cast<uintptr_t>(o) & 15) == 0) {
-              const int nvec = valid >> 2;
-              for (int i = row; i < nvec; i += 128)
-                reinterpret_cast<float4*>(o)[i] = reinterpret_cast<const float4*>(stage)[i];
-              for (int i = (nvec << 2) + row; i < valid; i += 128) o[i] = stage[i];
-            } else {
-              for (int i = row; i < valid; i += 128) o[i] = stage[i];
-            }
+            store_tile_probs(P.out + (P.split ? (long long)t0 * P.n * C : 0ll) + first * C, stage, (int)rows * C, row);
           }
           named_bar_sync(BAR_SOFTMAX, 128);                       // staging buffer free again
         }
@@ -882,7 +748,22 @@ void fused_release(rfk_mlp* h) {
   h->fused = nullptr;
 }
 
-size_t fused_workspace_bytes(int w, int n_classes, int64_t n) {
+bool fused_images(const rfk_mlp* h, FusedImages* out) {
+  const FusedState* s = static_cast<const FusedState*>(h->fused);
+  if (s == nullptr) return false;
+  out->w1 = s->dev.w1;
+  out->w2 = s->dev.w2;
+  out->w3 = s->dev.w3;
+  out->bias = s->dev.bias;
+  out->h1_pad = s->dev.h1_pad;
+  out->h2_pad = s->dev.h2_pad;
+  out->n_hidden = s->dev.n_hidden;
+  return true;
+}
+
+size_t fused_workspace_bytes(int w, int n_classes, int64_t n, int d) {
+  // large batches: the pair kernel writes per-trial probabilities for kernel 3
+  if (pair_applicable(d, n)) return pair_workspace_bytes(w, n_classes, n);
   // split mode (see the kernel): used when all (tile, trial) items fit on the GPU at once
   const int64_t n_tiles = (n + TILE_M - 1) / TILE_M;
   if (w > 1 && n_tiles * w <= (int64_t)num_sms()) return (size_t)w * (size_t)n * n_classes * sizeof(float);
@@ -893,6 +774,11 @@ int fused_forward(rfk_mlp* const* trials, int w, int total_trials, const uint8_t
                   void* ws, size_t ws_bytes, cudaStream_t st) {
   RFK_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0, "fused forward: x must be 16-byte aligned");
   const int d = trials[0]->d;
+  // large batches go to the CTA-pair kernel (weights resident in shared memory); an ensemble needs the
+  // per-trial scratch for that, without it the single-CTA kernel below still answers
+  if (pair_applicable(d, n) &&
+      (w == 1 || (ws != nullptr && ws_bytes >= pair_workspace_bytes(w, trials[0]->n_classes, n))))
+    return pair_forward(trials, w, total_trials, x, n, out, ws, ws_bytes, st);
   // TMA descriptor of the query batch: uint8 [n, d]; one box = 128 rows x 128 bytes, 128-byte swizzle
   CUtensorMap x_map;
   {
@@ -920,7 +806,7 @@ int fused_forward(rfk_mlp* const* trials, int w, int total_trials, const uint8_t
   }
   const int sms = num_sms();
   int grid = P.n_tiles < sms ? P.n_tiles : sms;
-  const size_t split_bytes = fused_workspace_bytes(w, P.n_classes, n);
+  const size_t split_bytes = w > 1 && (int64_t)P.n_tiles * w <= (int64_t)sms ? (size_t)w * (size_t)n * P.n_classes * sizeof(float) : 0;
   const bool split = split_bytes != 0 && ws != nullptr && ws_bytes >= split_bytes && getenv("RFK_NO_SPLIT") == nullptr;
   if (split) {
     P.split = 1;

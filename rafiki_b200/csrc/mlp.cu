@@ -212,7 +212,7 @@ extern "C" int rfk_ensemble_workspace_bytes(rfk_mlp_t* const* trials, int w, int
               "ensemble_workspace_bytes: bad argument");
   for (int t = 0; t < w; ++t) RFK_REQUIRE(trials[t] != nullptr, "ensemble_workspace_bytes: trials[%d] is NULL", t);
   if (all_fusable(trials, w)) {
-    *out = rfk::fused_workspace_bytes(w, trials[0]->n_classes, n);
+    *out = rfk::fused_workspace_bytes(w, trials[0]->n_classes, n, trials[0]->d);
     return RFK_OK;
   }
   // unfused: one probs buffer per trial + the largest per-trial scratch (trials run in turn)

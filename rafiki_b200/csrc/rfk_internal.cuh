@@ -22,9 +22,25 @@ int fused_prepare(rfk_mlp* h);
 void fused_release(rfk_mlp* h);
 // out = sum_w probs_w / total_trials over the w trials given (w == total_trials: the mean)
 // optional scratch of fused_workspace_bytes() enables the one-item-per-SM schedule for small batches
-size_t fused_workspace_bytes(int w, int n_classes, int64_t n);
+size_t fused_workspace_bytes(int w, int n_classes, int64_t n, int d);
 int fused_forward(rfk_mlp* const* trials, int w, int total_trials, const uint8_t* x, int64_t n,
                   float* out, void* ws, size_t ws_bytes, cudaStream_t st);
+
+// device images of a trial packed for the fused kernels (owned by the handle)
+struct FusedImages {
+  const uint8_t* w1;
+  const uint8_t* w2;
+  const uint8_t* w3;
+  const float* bias;
+  int h1_pad, h2_pad, n_hidden;
+};
+bool fused_images(const rfk_mlp* h, FusedImages* out);
+
+// fused_pair.cu -- CTA-pair kernel for large batches (weights resident in shared memory, trial-outer order)
+bool pair_applicable(int d, int64_t n);
+size_t pair_workspace_bytes(int w, int n_classes, int64_t n);
+int pair_forward(rfk_mlp* const* trials, int w, int total_trials, const uint8_t* x, int64_t n, float* out, void* ws,
+                 size_t ws_bytes, cudaStream_t st);
 
 // ensemble.cu
 int scale_inplace(float* p, int64_t count, double divisor, cudaStream_t st);

@@ -11,6 +11,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdio.h>
 
 namespace sm100 {
 
@@ -301,6 +302,78 @@ __device__ __forceinline__ void mma_commit_elect(uint64_t* bar) {
 __device__ __forceinline__ void mma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
                : "memory");
+}
+
+
+// ------------------------------------------------------------------ CTA pairs (cluster of two, cta_group::2)
+// Two CTAs on the SMs of one TPC act as one 256-row tile: ONE thread of the leader CTA (cluster
+// rank 0) issues each tcgen05.mma; every CTA supplies its own 128 rows of A (tensor memory) and of
+// D (tensor memory) and HALF of the B operand's N rows from its own shared memory, at the same
+// offsets in both CTAs.  Completion is multicast to the same mbarrier offset in both CTAs.
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {   // every thread of both CTAs
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// shared::cta address -> the same offset in CTA `rank` of the cluster (shared::cluster window)
+__device__ __forceinline__ uint32_t map_to_cta(uint32_t smem_addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_addr), "r"(rank));
+  return r;
+}
+// Arrive on an mbarrier of any CTA of the cluster (address from map_to_cta).  Default semantics
+// (release at CTA scope): what crosses the pair here is tensor-memory state, ordered by the tcgen05
+// fences around the arrive and the wait.  The .release.cluster / .acquire.cluster forms compile to
+// MEMBAR.ALL.GPU and CCTL.IVALL (an L1 invalidate) per call and made every hand-off several times slower.
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+template <int kCols>
+__device__ __forceinline__ void tmem_alloc_pair(uint32_t* smem_slot) {  // one full warp, the same warp index in both CTAs
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_slot)),
+               "n"(kCols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+template <int kCols>
+__device__ __forceinline__ void tmem_dealloc_pair(uint32_t taddr) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(kCols) : "memory");
+}
+// mma4_f16_ts_elect for a CTA pair (M = 256): leader CTA only
+__device__ __forceinline__ void mma4_f16_ts_pair_elect(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc,
+                                                        uint32_t accumulate_first, int nsteps) {
+  asm volatile(
+      "{\n\t.reg .pred p, q, q2, q3, q4, t;\n\t"
+      ".reg .b64 b2, b3, b4;\n\t"
+      ".reg .b32 a2, a3, a4;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "setp.eq.u32 t, 0, 0;\n\t"
+      "setp.gt.and.s32 q2, %5, 1, q;\n\t"
+      "setp.gt.and.s32 q3, %5, 2, q;\n\t"
+      "setp.gt.and.s32 q4, %5, 3, q;\n\t"
+      "add.u32 a2, %1, 8;\n\tadd.u64 b2, %2, 2;\n\t"
+      "add.u32 a3, %1, 16;\n\tadd.u64 b3, %2, 4;\n\t"
+      "add.u32 a4, %1, 24;\n\tadd.u64 b4, %2, 6;\n\t"
+      "@q  tcgen05.mma.cta_group::2.kind::f16 [%0], [%1], %2, %3, p;\n\t"
+      "@q2 tcgen05.mma.cta_group::2.kind::f16 [%0], [a2], b2, %3, t;\n\t"
+      "@q3 tcgen05.mma.cta_group::2.kind::f16 [%0], [a3], b3, %3, t;\n\t"
+      "@q4 tcgen05.mma.cta_group::2.kind::f16 [%0], [a4], b4, %3, t;\n\t}" ::"r"(d_tmem),
+      "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate_first), "r"(nsteps)
+      : "memory");
+}
+// completion of the leader's earlier MMAs -> the mbarrier at this offset in BOTH CTAs of the pair
+__device__ __forceinline__ void mma_commit_pair_elect(uint64_t* bar) {
+  asm volatile(
+      "{\n\t.reg .pred q;\n\t.reg .b16 m;\n\t"
+      "mov.b16 m, 3;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
+      "@q tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], m;\n\t}" ::"r"(
+          smem_u32(bar))
+      : "memory");
 }
 
 __device__ __forceinline__ bool elect_one() {
