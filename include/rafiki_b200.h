@@ -120,7 +120,9 @@ int rfk_mlp_forward(rfk_mlp_t* h, const uint8_t* x, int64_t n, float* probs, voi
  * The intermediate activations go to a block of RFK_STATIC_SCRATCH_BYTES that is part of the
  * library image on each GPU, so the call takes no workspace and calls no allocator.  A batch
  * whose rfk_mlp_workspace_bytes exceeds that block is refused with RFK_ERR_INVALID.  The
- * first call on a device resolves the block's address: make it before any stream capture.
+ * first call on a device resolves the block's address (and, under CUDA's lazy module loading, may
+ * be the moment the driver places the block on the GPU): make it before any stream capture.  The
+ * address is cached per device and does not survive cudaDeviceReset.
  * All calls on a GPU share the block: do not let two of them overlap in time.
  */
 #define RFK_STATIC_SCRATCH_BYTES (4 * 1024 * 1024)

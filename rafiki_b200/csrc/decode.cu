@@ -8,6 +8,7 @@
 // Design: persistent CTAs (a multiple of the SM count), the per-feature scale/shift
 // vectors staged once per CTA in shared memory, one 16-byte load (16 pixels) per thread
 // per step, 16-byte stores, streaming cache hints on both sides.
+#include <atomic>
 #include <type_traits>
 
 #include "rfk_common.cuh"
@@ -311,12 +312,13 @@ extern "C" int rfk_resize_decode_u8(const uint8_t* x, void* y, int64_t n, int s_
       const size_t smem = (size_t)((2 * d + 15) / 16) * 16 + (size_t)group * d_in;
       const int64_t n_groups = (n + group - 1) / group;
       const int g = (int)(n_groups < (int64_t)sms * 4 ? n_groups : (int64_t)sms * 4);
-      static bool attr_set[64] = {false};
+      static std::atomic<bool> attr_set[64];
       int dev = 0;
       RFK_CUDA_TRY(cudaGetDevice(&dev));
-      if (!attr_set[dev & 63]) {
+      RFK_REQUIRE(dev >= 0 && dev < 64, "resize: device ordinal %d not supported", dev);
+      if (!attr_set[dev].load(std::memory_order_acquire)) {     // setting it twice is harmless
         RFK_CUDA_TRY(cudaFuncSetAttribute(resize_u8_staged_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-        attr_set[dev & 63] = true;
+        attr_set[dev].store(true, std::memory_order_release);
       }
       resize_u8_staged_kernel<<<g, kThreads, smem, reinterpret_cast<cudaStream_t>(stream)>>>(
           x, static_cast<uint8_t*>(y), n, s_in, s_out, ch, group);

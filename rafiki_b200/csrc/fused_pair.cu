@@ -24,6 +24,8 @@
 // a multicast load: every CTA fetches its own bytes.
 #include <stdlib.h>
 
+#include <atomic>
+
 #include "fused_common.cuh"
 #include "pack.cuh"
 #include "rfk_internal.cuh"
@@ -643,8 +645,11 @@ int pair_forward(rfk_mlp* const* trials, int w, int total_trials, const uint8_t*
     RFK_CUDA_TRY(cudaMemsetAsync(dtrace, 0, trace_elems * sizeof(long long), st));
     P.trace = dtrace;
   }
-  static bool attr_set = false;
-  if (!attr_set) {
+  int dev = 0;
+  RFK_CUDA_TRY(cudaGetDevice(&dev));
+  RFK_REQUIRE(dev >= 0 && dev < 64, "pair kernel: device ordinal %d not supported", dev);
+  static std::atomic<bool> attr_set[64];
+  if (!attr_set[dev].load(std::memory_order_acquire)) {     // per device; setting it twice is harmless
     RFK_CUDA_TRY(cudaFuncSetAttribute(fused_pair_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_MAX));
     RFK_CUDA_TRY(cudaFuncSetAttribute(fused_pair_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_MAX));
     RFK_CUDA_TRY(cudaFuncSetAttribute(fused_pair_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_MAX));
@@ -655,7 +660,7 @@ int pair_forward(rfk_mlp* const* trials, int w, int total_trials, const uint8_t*
                 kRegsLaunch);
       return RFK_ERR_UNSUPPORTED;
     }
-    attr_set = true;
+    attr_set[dev].store(true, std::memory_order_release);
   }
   const long long items = (long long)w * P.n_pt;
   int pairs = num_sms() / 2;

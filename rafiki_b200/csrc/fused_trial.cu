@@ -54,6 +54,8 @@
 // bf16 (RFK_BF16); accumulation is fp32 in TMEM either way.
 #include <stdlib.h>
 
+#include <atomic>
+
 #include "pack.cuh"
 #include "rfk_internal.cuh"
 #include "sm100.cuh"
@@ -724,15 +726,17 @@ int fused_prepare(rfk_mlp* h) {
       return RFK_ERR_UNSUPPORTED;
     }
   }
-  static bool attr_set[64] = {false};
-  if (!attr_set[h->device & 63]) {
+  RFK_REQUIRE(h->device >= 0 && h->device < 64, "fused path: device ordinal %d not supported", h->device);
+  static std::atomic<bool> attr_set[64];
+  if (!attr_set[h->device].load(std::memory_order_acquire)) {     // setting it twice is harmless
+
     RFK_CUDA_TRY(cudaFuncSetAttribute(fused_ensemble_kernel<true, false>,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
     RFK_CUDA_TRY(cudaFuncSetAttribute(fused_ensemble_kernel<false, false>,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
     RFK_CUDA_TRY(cudaFuncSetAttribute(fused_ensemble_kernel<true, true>,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-    attr_set[h->device & 63] = true;
+    attr_set[h->device].store(true, std::memory_order_release);
   }
   return RFK_OK;
 }

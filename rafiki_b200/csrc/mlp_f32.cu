@@ -180,12 +180,16 @@ int mlp_f32_forward(rfk_mlp* h, const uint8_t* x, int64_t n, float* probs, void*
 //
 // What a caller should know:
 //  * The scratch is RFK_STATIC_SCRATCH_BYTES (4 MiB) of device memory per GPU, held from the
-//    moment the library is loaded on that GPU until the process exits.
+//    moment this part of the library is loaded on that GPU until the process exits.  With CUDA's
+//    default lazy module loading that moment can be the FIRST call on the device: the driver then
+//    places the module (the 4 MiB block included) on the GPU inside that call, which is an
+//    implicit allocation and may synchronise the device.  Later calls allocate nothing.
 //  * A batch whose activations do not fit (two ping-pong buffers of n x widest-layer floats,
 //    the figure rfk_mlp_workspace_bytes reports) is refused with RFK_ERR_INVALID; split it.
 //  * The first call on each device looks up the device address of the scratch block
 //    (cudaGetSymbolAddress) with that device current, and remembers it.  Make that first call
-//    before starting any stream capture on the device.
+//    before starting any stream capture on the device.  The remembered address does not survive
+//    cudaDeviceReset: a process that resets a device must not call this entry point on it again.
 //  * Every call on a device uses the same block and leaves its activations behind in it.  Nothing
 //    in it has to start at zero: each element that a kernel reads was written earlier in the same
 //    call.  Two calls that overlap in time on one GPU (different streams, or different threads)

@@ -283,6 +283,41 @@ def test_whole_tile_schedule_heterogeneous_trials_batch_20000():
         t.close()
 
 
+@pytest.mark.parametrize('S,n,w', [(28, 20000, 3), (32, 9700, 2), (28, 9473, 1)])
+def test_pair_kernel_equals_the_single_cta_kernel(S, n, w, monkeypatch):
+    """Large batches run on CTA pairs (tcgen05 cta_group::2, weights resident in shared memory, trial-outer
+    order, kernel 3 over per-trial outputs); RFK_NO_PAIR=1 sends the same call to the single-CTA kernel
+    (weights streamed, ensemble sum in registers).  Same arithmetic, same bits -- and both against the oracle."""
+    d = S * S
+    dead = synth.dead_mask(d)
+    shapes = [(2, 128), (1, 36), (2, 77)]
+    params = [synth.make_trial(t, S, 1, *shapes[t], dead=dead, data_kind='fashion') for t in range(w)]
+    X = synth.make_queries(n, S, 1, 'fashion', seed=31, dead=dead)
+    x = torch.from_numpy(X).cuda()
+    trials = [engine.Trial(p) for p in params]
+    ens = engine.Ensemble(trials)
+    before = _native.launch_count('fused_pair')
+    pair = ens.forward(x).clone()
+    assert _native.launch_count('fused_pair') == before + 1          # the pair kernel really ran
+    monkeypatch.setenv('RFK_NO_PAIR', '1')
+    single = ens.forward(x).clone()
+    monkeypatch.delenv('RFK_NO_PAIR')
+    assert _native.launch_count('fused_pair') == before + 1
+    assert torch.equal(pair, single)
+    sl = slice(n - 600, n)
+    want = ff.ensemble_mean_array([ff.forward(p, X[sl], np.float32) for p in params])
+    assert np.abs(pair[sl].cpu().numpy().astype(np.float64) - want).max() <= TOL_TC
+    # without scratch an ensemble still gets its answer (single-CTA kernel), and the same one
+    if w > 1:
+        out = torch.empty_like(pair)
+        hs = _native.handle_array([t.handle for t in trials])
+        _native.check(_native.load().rfk_ensemble_forward(hs, w, w, x.data_ptr(), n, out.data_ptr(), None, 0, None))
+        torch.cuda.synchronize()
+        assert torch.equal(out, pair)
+    for t in trials:
+        t.close()
+
+
 @pytest.mark.parametrize('n', [65536, 20000])
 def test_fused_kernel_gives_the_same_bits_on_every_launch(n):
     """Row-independent predict (TfFeedForward.py:95) and a deterministic mean (ensemble.py:13-14):
