@@ -70,21 +70,29 @@ ensemble_mean_scalar_kernel(const TrialPtrs ptrs, int w, int64_t n_elems, float*
 }  // namespace
 
 namespace {
-int ensemble_reduce(const float* const* probs, int w, int64_t n, int c, float* out, void* stream, bool mean);
+int ensemble_reduce(const float* const* probs, int w, int64_t n, int c, float* out, void* stream, double divisor);
 }
 
 extern "C" int rfk_ensemble_mean(const float* const* probs, int w, int64_t n, int c, float* out,
                                  void* stream) {
-  return ensemble_reduce(probs, w, n, c, out, stream, true);
+  return ensemble_reduce(probs, w, n, c, out, stream, (double)w);
 }
 
 extern "C" int rfk_ensemble_sum(const float* const* probs, int w, int64_t n, int c, float* out, void* stream) {
-  return ensemble_reduce(probs, w, n, c, out, stream, false);
+  return ensemble_reduce(probs, w, n, c, out, stream, 1.0);
 }
 
+namespace rfk {
+// out = float(sum over the w inputs in float64 / divisor): the partial mean of a rank that holds w of
+// `divisor` trials, in one kernel and one rounding
+int ensemble_partial_mean(const float* const* probs, int w, int64_t n, int c, float* out, double divisor,
+                          cudaStream_t st) {
+  return ensemble_reduce(probs, w, n, c, out, st, divisor);
+}
+}  // namespace rfk
+
 namespace {
-int ensemble_reduce(const float* const* probs, int w, int64_t n, int c, float* out, void* stream, bool mean) {
-  const double divisor = mean ? (double)w : 1.0;
+int ensemble_reduce(const float* const* probs, int w, int64_t n, int c, float* out, void* stream, double divisor) {
   RFK_REQUIRE(w >= 1 && w <= RFK_MAX_TRIALS, "ensemble_mean: w=%d outside 1..%d", w, RFK_MAX_TRIALS);
   RFK_REQUIRE(n >= 0 && c >= 1, "ensemble_mean: bad shape n=%lld c=%d", (long long)n, c);
   if (n == 0) return RFK_OK;

@@ -91,9 +91,12 @@ struct PairParams {
   long long trial_stride;     // elements between the outputs of consecutive trials (0: a single trial)
   long long n;
   double divisor;             // the stored value is float(p / divisor)
+  float div_f, div_recip;     // divisor as float, and 1 / divisor when it is a power of two
+  int div_pow2;
   int d, n_kb, n_atoms, w, n_classes, n_pt, raw_stages;
   int items_q, items_r;       // items per pair: pair p takes items_q (+ 1 if p < items_r), in order
   int off_w2, off_w3, off_raw, off_bias, off_out, off_bar;
+  rfk::PeerHook hook;   // all zero: no hand-shake (see rfk_internal.cuh)
   int debug;            // development (RFK_PAIR_DEBUG): 4 = skip the layer-1 MMAs
   long long* trace;     // development (RFK_PAIR_TRACE): event timestamps of pair 0, [2 CTAs][5 roles][kTraceLen]
 };
@@ -240,6 +243,7 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
     const float* bias = reinterpret_cast<const float*>(smem + P.off_bias);
     uint32_t v3[16];
     bool have_prev = false;
+    bool may_store = P.hook.n_wait == 0;      // output in a peer's memory: wait until the slots have been consumed
     int prev_t = 0, prev_pt = 0;
     auto finish_prev = [&]() {
       // logits (v3) + bias -> softmax -> this trial's probabilities, staged and stored with 16-byte stores
@@ -249,22 +253,49 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
         const int C = P.n_classes;
         const float* stage = reinterpret_cast<const float*>(smem + P.off_out);
         const uint32_t dst = smem_base + (uint32_t)P.off_out + (uint32_t)(row * C) * 4u;
-        // a lone trial of a larger ensemble stores float(p / total) rounded once from float64 (what the
-        // single-CTA kernel stores); per-trial outputs for kernel 3 are stored as they are -- a float64
-        // division costs thousands of cycles per tile and must stay off that path
+        // A lone trial of a larger ensemble (one trial per GPU) stores float(p / total) with ONE rounding of the
+        // exact quotient, which is what the single-CTA kernel's float64 division gives for at most 32 trials.
+        // A power-of-two total is an exact scaling; otherwise one correctly rounded float division.  (The
+        // float64 division itself costs ~10 us per launch on this path and must stay off it.)
         if (P.divisor == 1.0) {
 #pragma unroll
           for (int j = 0; j < CPAD; ++j) sts_f32_if(dst + 4u * j, z[j] * inv, j < C);
+        } else if (P.div_pow2) {
+#pragma unroll
+          for (int j = 0; j < CPAD; ++j) sts_f32_if(dst + 4u * j, (z[j] * inv) * P.div_recip, j < C);
         } else {
 #pragma unroll
-          for (int j = 0; j < CPAD; ++j) sts_f32_if(dst + 4u * j, (float)((double)(z[j] * inv) / P.divisor), j < C);
+          for (int j = 0; j < CPAD; ++j) sts_f32_if(dst + 4u * j, __fdiv_rn(z[j] * inv, P.div_f), j < C);
+        }
+        if (!may_store) {
+          if (lane == 0) {
+            const long long t0 = clock64();
+            for (int q = 0; q < P.hook.n_wait; ++q) {
+              unsigned int v;
+              do {
+                asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(P.hook.wait_flags + q) : "memory");
+                if (clock64() - t0 > 4000000000LL) {
+                  printf("rafiki_b200: pair kernel timed out waiting for its output slot (block %d)\n", blockIdx.x);
+                  __trap();
+                }
+              } while ((int)(v - P.hook.wait_value) < 0);
+            }
+          }
+          __syncwarp();
+          may_store = true;
         }
         named_bar_sync(BAR_SOFTMAX, 128);
         {
           const long long first = (long long)prev_pt * (2 * TILE_M) + (long long)rank * TILE_M;
           long long rows = P.n - first;
           rows = rows < 0 ? 0 : (rows < TILE_M ? rows : TILE_M);
-          store_tile_probs(P.out + (long long)prev_t * P.trial_stride + first * C, stage, (int)rows * C, row);
+          float* obase = P.out + (long long)prev_t * P.trial_stride;
+          if (P.hook.n_owner > 0) {                  // scatter form: this tile's rows belong to one owner GPU
+            int j = 0;
+            while (j + 1 < P.hook.n_owner && prev_pt >= P.hook.owner_bound[j + 1]) ++j;
+            obase = P.hook.out_owner[j];
+          }
+          store_tile_probs(obase + first * C, stage, (int)rows * C, row);
         }
         named_bar_sync(BAR_SOFTMAX, 128);
       }
@@ -457,6 +488,59 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
         cur_t = it.t;
       }
     }
+    // =============================================================== carried cross-GPU reduction (see PeerHook)
+    // This warp is idle for the rest of the launch.  In the trial-per-GPU deployment it adds, for the rows
+    // this GPU owns, the partial means every rank stored here during the PREVIOUS step (float64, rank order,
+    // one rounding) and stores them into the root's result: the collective rides inside the next trial
+    // kernel instead of standing between two of them.
+    if (P.hook.n_carry > 0) {
+      const int G = P.hook.n_carry;
+      if (lane < G) {
+        const long long t0 = clock64();
+        unsigned int v;
+        do {
+          asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(P.hook.carry_arrived + lane) : "memory");
+          if (clock64() - t0 > 4000000000LL) {
+            printf("rafiki_b200: carried reduction timed out waiting for rank %d (block %d)\n", lane, blockIdx.x);
+            __trap();
+          }
+        } while ((int)(v - P.hook.carry_step) < 0);
+      }
+      __syncwarp();
+      const long long span = P.hook.carry_v_hi - P.hook.carry_v_lo;
+      const long long per = (span + gridDim.x - 1) / gridDim.x;
+      const long long lo = P.hook.carry_v_lo + per * blockIdx.x;
+      const long long hi = lo + per < P.hook.carry_v_hi ? lo + per : P.hook.carry_v_hi;
+      for (long long i = lo + lane; i < hi; i += 32) {
+        double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+        for (int j0 = 0; j0 < G; j0 += 4) {          // four slots in flight (the warp has 56 registers)
+          float4 v[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u)
+            if (j0 + u < G) v[u] = __ldcg(reinterpret_cast<const float4*>(P.hook.carry_slot[j0 + u]) + i);
+#pragma unroll
+          for (int u = 0; u < 4; ++u)
+            if (j0 + u < G) {
+              s0 += (double)v[u].x; s1 += (double)v[u].y; s2 += (double)v[u].z; s3 += (double)v[u].w;
+            }
+        }
+        float4 o;
+        o.x = (float)s0; o.y = (float)s1; o.z = (float)s2; o.w = (float)s3;
+        reinterpret_cast<float4*>(P.hook.carry_out)[i] = o;
+      }
+      __syncwarp();
+      if (lane == 0) {
+        __threadfence_system();
+        if (atomicAdd(P.hook.carry_counter, 1u) == gridDim.x - 1) {      // last CTA: all my rows are in place
+          atomicExch(P.hook.carry_counter, 0u);
+          __threadfence_system();
+          asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(P.hook.carry_done), "r"(P.hook.carry_step) : "memory");
+          for (int j = 0; j < G; ++j)
+            asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(P.hook.carry_consumed[j]), "r"(P.hook.carry_step)
+                         : "memory");
+        }
+      }
+    }
   } else if (warp == WARP_MMA && leader) {
     // =============================================================== layer-1 MMA issuer (leader CTA, for the pair)
     // A: tensor memory of each CTA (its own 128 rows); B: each CTA's half of W1, resident; D: tensor
@@ -538,12 +622,32 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
   tc_fence_before_sync();
   cluster_sync_all();            // neither CTA leaves (or frees tensor memory) while the other may still signal it
   if (warp == WARP_MMA) tmem_dealloc_pair<TMEM_COLS>(tmem_base);
+  if (P.hook.n_signal > 0 && threadIdx.x == 0) {
+    // every output store of this CTA precedes the cluster barrier above; the last CTA out publishes the step
+    __threadfence_system();
+    if (atomicAdd(P.hook.counter, 1u) == gridDim.x - 1) {
+      atomicExch(P.hook.counter, 0u);
+      __threadfence_system();
+      for (int q = 0; q < P.hook.n_signal; ++q)
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(P.hook.signal_flags[q]), "r"(P.hook.signal_value) : "memory");
+    }
+  }
 }
 
 }  // namespace
 
 // ------------------------------------------------------------------------------- host side
 namespace rfk {
+
+namespace {
+thread_local PeerHook g_hook;
+thread_local bool g_hook_set = false;
+}  // namespace
+void set_peer_hook(const PeerHook* hook) {
+  g_hook_set = hook != nullptr;
+  if (hook != nullptr) g_hook = *hook;
+}
+bool peer_hook_pending() { return g_hook_set; }
 
 namespace {
 constexpr int kMinPairTiles = 37;     // below this the single-CTA kernel's finer tiles fill the GPU better
@@ -627,6 +731,13 @@ int pair_forward(rfk_mlp* const* trials, int w, int total_trials, const uint8_t*
     P.out = out;
     P.trial_stride = 0;
     P.divisor = (double)total_trials;
+    P.div_f = (float)total_trials;
+    P.div_pow2 = (total_trials & (total_trials - 1)) == 0 ? 1 : 0;
+    P.div_recip = 1.0f / (float)total_trials;
+    if (g_hook_set) {          // the kernel itself waits for / publishes the peer hand-shake
+      P.hook = g_hook;
+      g_hook_set = false;
+    }
   } else {
     P.out = static_cast<float*>(ws);
     P.trial_stride = (long long)n * C;
@@ -694,9 +805,8 @@ int pair_forward(rfk_mlp* const* trials, int w, int total_trials, const uint8_t*
   if (w > 1) {
     const float* ptrs[RFK_MAX_TRIALS];
     for (int t = 0; t < w; ++t) ptrs[t] = static_cast<const float*>(ws) + (size_t)t * (size_t)n * C;
-    int rc = rfk_ensemble_mean(ptrs, w, n, C, out, st);
-    if (rc != RFK_OK) return rc;
-    if (total_trials != w) return scale_inplace(out, n * (int64_t)C, (double)total_trials / (double)w, st);
+    // float64 sum in trial order, divided by the size of the WHOLE ensemble, one rounding
+    return ensemble_partial_mean(ptrs, w, n, C, out, (double)total_trials, st);
   }
   return RFK_OK;
 }

@@ -864,9 +864,7 @@ int fused_forward(rfk_mlp* const* trials, int w, int total_trials, const uint8_t
     // kernel 3 over the W per-trial outputs: same float64 sum and rounding as the in-kernel mean
     const float* ptrs[RFK_MAX_TRIALS];
     for (int t = 0; t < w; ++t) ptrs[t] = static_cast<const float*>(ws) + (size_t)t * (size_t)n * P.n_classes;
-    int rc = rfk_ensemble_mean(ptrs, w, n, P.n_classes, out, st);
-    if (rc != RFK_OK) return rc;
-    if (total_trials != w) return scale_inplace(out, n * (int64_t)P.n_classes, (double)total_trials / (double)w, st);
+    return ensemble_partial_mean(ptrs, w, n, P.n_classes, out, (double)total_trials, st);
   }
   return RFK_OK;
 }

@@ -18,6 +18,7 @@
 // Flags are monotonic step counters, so nothing is ever reset; buffers are double buffered by
 // step parity by the caller (rafiki_b200/distributed.py).  Every spin is bounded: a rank that
 // died makes the others trap after ~2 s instead of hanging the box.
+#include <stdlib.h>
 #include <string.h>
 
 #include "rfk_internal.cuh"
@@ -241,14 +242,15 @@ extern "C" int rfk_peer_wait(const unsigned int* flags_of_this_rank, int world, 
 // every rank, the layout and the step counters, so that one C call enqueues a whole step:
 //   [all-gather of the uint8 query slices over NVLink]  ->  fused trial kernel  ->  cross-rank mean.
 // Block layout (the same on every rank, so each rank can compute every peer's addresses):
-//   partial[2] | result[2] | queries[2] | flags
+//   partial[2] | result[2] | queries[2] | slots[2][world] | flags
 // where partial / result hold max_n * n_classes floats, queries max_n * d bytes, all rounded up to
-// 256 bytes, and flags = 3 * world + 1 uint32: [0,G) "partials ready", [G,2G) "slice in place",
-// [2G] block counter, [2G+1, 3G+1) "query slice ready".
+// 256 bytes, `slots` (2 x world buffers: where each rank's kernel stores its partial means on the root)
+// and the flag words listed in peer_layout().
 namespace {
 
 struct PeerLayout {
-  size_t buf_bytes, x_bytes, off_partial[2], off_result[2], off_x[2], off_flags, total;
+  size_t buf_bytes, x_bytes, off_partial[2], off_result[2], off_x[2], off_slots[2], off_flags, total;
+  int f_arrived, f_consumed, f_counter, f_sumcounter, f_done;    // indices into the flag words (see below)
 };
 
 PeerLayout peer_layout(int world, int64_t max_n, int d, int n_classes) {
@@ -259,8 +261,18 @@ PeerLayout peer_layout(int world, int64_t max_n, int d, int n_classes) {
   for (int k = 0; k < 2; ++k) { L.off_partial[k] = off; off += L.buf_bytes; }
   for (int k = 0; k < 2; ++k) { L.off_result[k] = off; off += L.buf_bytes; }
   for (int k = 0; k < 2; ++k) { L.off_x[k] = off; off += L.x_bytes; }
+  for (int k = 0; k < 2; ++k) { L.off_slots[k] = off; off += (size_t)world * L.buf_bytes; }   // one slot per rank (used on the root)
   L.off_flags = off;
-  off += ((size_t)(3 * world + 1) * sizeof(unsigned int) + 255) / 256 * 256;
+  // flag words: [0,G) partials ready | [G,2G) slice in place | [2G] block counter | [2G+1,3G+1) query slice ready |
+  //             [3G+1,4G+1) rank's partial means have arrived in its slot (on every owner) | [4G+1,5G+1) owner j has
+  //             consumed its slots (on every rank) | [5G+1] block counter of the trial kernel | [5G+2] block counter of
+  //             the gather-sum kernel | [5G+3,6G+3) rank's rows of the result are in place (on the root)
+  L.f_arrived = 3 * world + 1;
+  L.f_consumed = 4 * world + 1;       // G words: owner j has consumed the slots it holds
+  L.f_counter = 5 * world + 1;
+  L.f_sumcounter = 5 * world + 2;
+  L.f_done = 5 * world + 3;           // G words (root): rank j's rows of the result are in place
+  off += ((size_t)(6 * world + 4) * sizeof(unsigned int) + 255) / 256 * 256;
   L.total = off;
   return L;
 }
@@ -312,6 +324,52 @@ peer_allgather_kernel(const GatherPtrs ptrs, uint8_t* __restrict__ mine_x, int w
 #pragma unroll
       for (int u = 0; u < 4; ++u)
         if (b + u * stride < ptrs.hi[j]) *reinterpret_cast<uint4*>(mine_x + b + u * stride) = v[u];
+    }
+  }
+}
+
+// Root side of the gather form: every rank's trial kernel has stored its partial means straight into
+// slot[rank] of THIS GPU's block (over NVLink, tile by tile while it computed) and raised arrived[rank].
+// One kernel waits for all ranks, adds the slots in float64 in rank order with one rounding (the same sum
+// as peer_reduce_kernel), and tells every rank that the slots of this step may be reused.
+struct SlotPtrs {
+  const float* slot[kMaxRanks];
+  unsigned int* consumed[kMaxRanks];    // each rank's "slot consumed" word (peer mapped)
+};
+__global__ void __launch_bounds__(kThreads)
+peer_gather_sum_kernel(const SlotPtrs ptrs, const unsigned int* arrived, int world, unsigned int step, long long v_lo,
+                       long long v_hi, float* __restrict__ out, unsigned int* counter, unsigned int* done_flag) {
+  if (threadIdx.x < world) {
+    if (!spin_until_ge(arrived + threadIdx.x, step)) {
+      printf("rafiki_b200: gather-sum timed out waiting for rank %d (step %u)\n", (int)threadIdx.x, step);
+      __trap();
+    }
+  }
+  __syncthreads();
+  const long long stride = (long long)gridDim.x * kThreads;
+  for (long long i = v_lo + (long long)blockIdx.x * kThreads + threadIdx.x; i < v_hi; i += stride) {
+    float4 v[kMaxRanks];
+#pragma unroll
+    for (int j = 0; j < kMaxRanks; ++j)
+      if (j < world) v[j] = __ldcg(reinterpret_cast<const float4*>(ptrs.slot[j]) + i);   // written by peers: bypass L1
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+#pragma unroll
+    for (int j = 0; j < kMaxRanks; ++j)
+      if (j < world) {
+        s0 += (double)v[j].x; s1 += (double)v[j].y; s2 += (double)v[j].z; s3 += (double)v[j].w;
+      }
+    float4 o;
+    o.x = (float)s0; o.y = (float)s1; o.z = (float)s2; o.w = (float)s3;
+    reinterpret_cast<float4*>(out)[i] = o;
+  }
+  __threadfence_system();      // `out` may be the root's memory
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    if (atomicAdd(counter, 1u) == gridDim.x - 1) {     // last block: every slot has been read, every row stored
+      atomicExch(counter, 0u);
+      __threadfence_system();
+      if (done_flag != nullptr) st_release_sys(done_flag, step);
+      for (int j = 0; j < world; ++j) st_release_sys(ptrs.consumed[j], step);
     }
   }
 }
@@ -417,14 +475,126 @@ extern "C" int rfk_peer_ensemble_step(rfk_peer_t* p, rfk_mlp_t* const* trials, i
   RFK_REQUIRE(x != nullptr, "peer_ensemble_step: x is NULL (pass the pointer rfk_peer_allgather_u8 returned)");
   const unsigned int step = ++p->rstep;
   const int k = (int)(step & 1);
-  float* partial = reinterpret_cast<float*>(p->base[p->rank] + p->L.off_partial[k]);
   const int64_t count = n * p->n_classes;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  static const bool reduce_mode = []() { const char* m = getenv("RFK_PEER_MODE"); return m != nullptr && m[0] == 'r'; }();
+  if (!reduce_mode) {
+    // Gather forms (default): a rank's trial kernel stores its partial means straight into slots in OTHER
+    // GPUs' blocks while it computes (16-byte stores over NVLink from its epilogue), so no communication
+    // kernel stands between two trial kernels.
+    //  * scatter (one trial per rank, batch large enough for the pair kernel): the rows of the batch are
+    //    divided among the ranks; every tile goes to the OWNER of its rows; each owner adds the G slots of
+    //    its rows (float64, rank order, one rounding) and stores the result rows into the root's buffer.
+    //    Every GPU does 1/G of the summing and no GPU waits for a slower one inside its trial kernel.
+    //  * fixed root (every other case): all slots live on the root, which adds them.
+    // Hand-shake per step s, slots double buffered by parity: a slot may be overwritten once its owner has
+    // consumed step s - 2; after its last store a rank raises arrived[rank] on every owner.
+    unsigned int* my_flags = reinterpret_cast<unsigned int*>(p->base[p->rank] + p->L.off_flags);
+    unsigned int* root_flags = reinterpret_cast<unsigned int*>(p->base[p->root] + p->L.off_flags);
+    const int G = p->world;
+    const bool scatter = w == 1 && total_trials == G && G > 1 && trials != nullptr && trials[0]->fusable &&
+                         trials[0]->dtype != RFK_F32 && rfk::pair_applicable(trials[0]->d, n);
+    const int n_pt = (int)((n + 255) / 256);
+    rfk::PeerHook hook;
+    memset(&hook, 0, sizeof(hook));
+    hook.wait_value = step >= 2 ? step - 2 : 0;
+    hook.signal_value = step;
+    hook.counter = my_flags + p->L.f_counter;
+    if (scatter) {
+      hook.wait_flags = my_flags + p->L.f_consumed;          // one word per owner
+      hook.n_wait = G;
+      hook.n_signal = G;
+      hook.n_owner = G;
+      for (int j = 0; j < G; ++j) {
+        hook.signal_flags[j] = reinterpret_cast<unsigned int*>(p->base[j] + p->L.off_flags) + p->L.f_arrived + p->rank;
+        hook.out_owner[j] = reinterpret_cast<float*>(p->base[j] + p->L.off_slots[k] + (size_t)p->rank * p->L.buf_bytes);
+        hook.owner_bound[j] = (int)((long long)n_pt * j / G);
+      }
+      hook.owner_bound[G] = n_pt;
+      rfk::set_peer_hook(&hook);
+      const int rc = rfk_ensemble_forward(trials, w, total_trials, x, n, hook.out_owner[p->rank], workspace, workspace_bytes,
+                                          stream);
+      if (rfk::peer_hook_pending()) {      // the call did not reach the pair kernel after all
+        rfk::set_peer_hook(nullptr);
+        rfk::set_error("peer_ensemble_step: internal routing error (hook not consumed)");
+        return RFK_ERR_INVALID;
+      }
+      if (rc != RFK_OK) return rc;
+      // my rows: add the G slots, store into the root's result, tell the root and free the slots
+      const long long row_lo = (long long)hook.owner_bound[p->rank] * 256, row_hi_ = (long long)hook.owner_bound[p->rank + 1] * 256;
+      const long long row_hi = row_hi_ < n ? row_hi_ : n;
+      SlotPtrs sp;
+      for (int j = 0; j < kMaxRanks; ++j) {
+        sp.slot[j] = nullptr;
+        sp.consumed[j] = nullptr;
+        if (j < G) {
+          sp.slot[j] = reinterpret_cast<const float*>(p->base[p->rank] + p->L.off_slots[k] + (size_t)j * p->L.buf_bytes);
+          sp.consumed[j] = reinterpret_cast<unsigned int*>(p->base[j] + p->L.off_flags) + p->L.f_consumed + p->rank;
+        }
+      }
+      float* res = reinterpret_cast<float*>(p->base[p->root] + p->L.off_result[k]);
+      const long long v_lo = row_lo * p->n_classes / 4, v_hi = (row_hi > row_lo ? row_hi : row_lo) * p->n_classes / 4;
+      const long long want = (v_hi - v_lo + kThreads - 1) / kThreads;
+      const int grid = (int)(want < 1 ? 1 : (want < (long long)p->grid_blocks ? want : (long long)p->grid_blocks));
+      peer_gather_sum_kernel<<<grid, kThreads, 0, st>>>(sp, my_flags + p->L.f_arrived, G, step, v_lo, v_hi, res,
+                                                        my_flags + p->L.f_sumcounter, root_flags + p->L.f_done + p->rank);
+      RFK_LAUNCH_CHECK("peer_gather_sum_kernel");
+      if (p->rank == p->root) {
+        const int rc2 = rfk_peer_wait_flags(root_flags + p->L.f_done, G, step, stream);
+        if (rc2 != RFK_OK) return rc2;
+      }
+      if (result != nullptr) *result = reinterpret_cast<float*>(p->base[p->rank] + p->L.off_result[k]);
+      return RFK_OK;
+    }
+    // ---- fixed root
+    float* slot = reinterpret_cast<float*>(p->base[p->root] + p->L.off_slots[k] + (size_t)p->rank * p->L.buf_bytes);
+    const unsigned int* wait_flag = my_flags + p->L.f_consumed + p->root;
+    unsigned int* signal_flag = root_flags + p->L.f_arrived + p->rank;
+    if (hook.wait_value > 0) {
+      const int rc = rfk_peer_wait_flags(wait_flag, 1, hook.wait_value, stream);
+      if (rc != RFK_OK) return rc;
+    }
+    if (w > 0) {
+      RFK_REQUIRE(trials != nullptr, "peer_ensemble_step: trials is NULL");
+      const int rc = rfk_ensemble_forward(trials, w, total_trials, x, n, slot, workspace, workspace_bytes, stream);
+      if (rc != RFK_OK) return rc;
+    } else {      // a rank that holds no trial (fewer trials than GPUs) contributes zeros
+      RFK_CUDA_TRY(cudaMemsetAsync(slot, 0, (size_t)count * sizeof(float), st));
+    }
+    {
+      unsigned int* sig[1] = {signal_flag};
+      const int rc = rfk_peer_signal(sig, 1, step, stream);
+      if (rc != RFK_OK) return rc;
+    }
+    if (p->rank == p->root) {
+      SlotPtrs sp;
+      for (int j = 0; j < kMaxRanks; ++j) {
+        sp.slot[j] = nullptr;
+        sp.consumed[j] = nullptr;
+        if (j < G) {
+          sp.slot[j] = reinterpret_cast<const float*>(p->base[p->root] + p->L.off_slots[k] + (size_t)j * p->L.buf_bytes);
+          sp.consumed[j] = reinterpret_cast<unsigned int*>(p->base[j] + p->L.off_flags) + p->L.f_consumed + p->root;
+        }
+      }
+      float* res = reinterpret_cast<float*>(p->base[p->root] + p->L.off_result[k]);
+      const long long n_vec = count / 4;
+      const long long want = (n_vec + kThreads - 1) / kThreads;
+      const int grid = (int)(want < (long long)p->grid_blocks * 4 ? want : (long long)p->grid_blocks * 4);
+      peer_gather_sum_kernel<<<grid, kThreads, 0, st>>>(sp, root_flags + p->L.f_arrived, G, step, 0, n_vec, res,
+                                                        root_flags + p->L.f_sumcounter, nullptr);
+      RFK_LAUNCH_CHECK("peer_gather_sum_kernel");
+    }
+    if (result != nullptr) *result = reinterpret_cast<float*>(p->base[p->rank] + p->L.off_result[k]);
+    return RFK_OK;
+  }
+  // Reduce-scatter form (RFK_PEER_MODE=reduce): partial means in local memory, every rank sums 1/G of the rows
+  float* partial = reinterpret_cast<float*>(p->base[p->rank] + p->L.off_partial[k]);
   if (w > 0) {
     RFK_REQUIRE(trials != nullptr, "peer_ensemble_step: trials is NULL");
     const int rc = rfk_ensemble_forward(trials, w, total_trials, x, n, partial, workspace, workspace_bytes, stream);
     if (rc != RFK_OK) return rc;
   } else {      // a rank that holds no trial (fewer trials than GPUs) contributes zeros
-    RFK_CUDA_TRY(cudaMemsetAsync(partial, 0, (size_t)count * sizeof(float), reinterpret_cast<cudaStream_t>(stream)));
+    RFK_CUDA_TRY(cudaMemsetAsync(partial, 0, (size_t)count * sizeof(float), st));
   }
   const float* probs[kMaxRanks];
   unsigned int* flags[kMaxRanks];

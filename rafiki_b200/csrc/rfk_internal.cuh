@@ -36,6 +36,46 @@ struct FusedImages {
 };
 bool fused_images(const rfk_mlp* h, FusedImages* out);
 
+// Optional hand-shake of a forward call whose output lies in ANOTHER GPU's memory (peer.cu: a rank's
+// kernel stores its partial means straight into the root's slot over NVLink).  Before its first output
+// store the kernel waits until *wait_flag >= wait_value (the root has consumed what the slot held); after
+// its last store it publishes signal_value in *signal_flag at system scope.  `counter` is a zero-initialised
+// word in local memory that the kernel leaves at zero.  Only the pair kernel's single-trial path takes
+// the hook inside the kernel; peer.cu brackets every other path with its own tiny kernels.
+constexpr int kPeerMaxRanks = 16;
+struct PeerHook {
+  // before the first output store: every one of the n_wait words at wait_flags is >= wait_value
+  const unsigned int* wait_flags;
+  int n_wait;
+  unsigned int wait_value;
+  // after the last output store: signal_value is published (system scope) in each of the n_signal words
+  unsigned int* signal_flags[kPeerMaxRanks];
+  int n_signal;
+  unsigned int signal_value;
+  unsigned int* counter;
+  // scatter form: the rows of pair tile pt go to out_owner[j] (a full-size [n, C] buffer in GPU j's memory,
+  // indexed by global row) for owner_bound[j] <= pt < owner_bound[j + 1]; n_owner == 0: the call's `out`
+  float* out_owner[kPeerMaxRanks];
+  int owner_bound[kPeerMaxRanks + 1];
+  int n_owner;
+  // Carried reduction: the sum of the PREVIOUS step's slots that this GPU owns, done by an otherwise idle warp
+  // of every CTA while the tensor cores work on this step (n_carry == 0: nothing to carry).  carry_slot[j] is
+  // rank j's slot in THIS GPU's memory; rows [carry_v_lo, carry_v_hi) in float4 units; the sums go to
+  // carry_out (the root's result buffer of that step), then carry_done (root) and carry_consumed[j] (every
+  // rank) receive carry_step.
+  const float* carry_slot[kPeerMaxRanks];
+  unsigned int* carry_consumed[kPeerMaxRanks];
+  const unsigned int* carry_arrived;
+  unsigned int* carry_done;
+  unsigned int* carry_counter;
+  float* carry_out;
+  long long carry_v_lo, carry_v_hi;
+  unsigned int carry_step;
+  int n_carry;
+};
+void set_peer_hook(const PeerHook* hook);     // thread-local; consumed (and cleared) by the next pair_forward with w == 1
+bool peer_hook_pending();
+
 // fused_pair.cu -- CTA-pair kernel for large batches (weights resident in shared memory, trial-outer order)
 bool pair_applicable(int d, int64_t n);
 size_t pair_workspace_bytes(int w, int n_classes, int64_t n);
@@ -44,5 +84,7 @@ int pair_forward(rfk_mlp* const* trials, int w, int total_trials, const uint8_t*
 
 // ensemble.cu
 int scale_inplace(float* p, int64_t count, double divisor, cudaStream_t st);
+int ensemble_partial_mean(const float* const* probs, int w, int64_t n, int c, float* out, double divisor,
+                          cudaStream_t st);
 
 }  // namespace rfk

@@ -307,6 +307,15 @@ def test_pair_kernel_equals_the_single_cta_kernel(S, n, w, monkeypatch):
     sl = slice(n - 600, n)
     want = ff.ensemble_mean_array([ff.forward(p, X[sl], np.float32) for p in params])
     assert np.abs(pair[sl].cpu().numpy().astype(np.float64) - want).max() <= TOL_TC
+    # one trial of a larger ensemble (what a rank holds when trials are placed one per GPU): float(p / total),
+    # the same bits from both kernels for a power-of-two total and for an odd one
+    for total in (8, 3):
+        part = engine.Ensemble(trials[:1], total_trials=total)
+        a = part.forward(x).clone()
+        monkeypatch.setenv('RFK_NO_PAIR', '1')
+        b = part.forward(x).clone()
+        monkeypatch.delenv('RFK_NO_PAIR')
+        assert torch.equal(a, b), 'total_trials = {}'.format(total)
     # without scratch an ensemble still gets its answer (single-CTA kernel), and the same one
     if w > 1:
         out = torch.empty_like(pair)

@@ -22,10 +22,11 @@ def _free_port():
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason='needs at least 2 GPUs')
-def test_peer_ensemble_equals_the_single_gpu_ensemble():
+@pytest.mark.parametrize('n_trials', [5, 2])      # 3 + 2 trials per rank; one trial per rank (hand-shake inside the kernel)
+def test_peer_ensemble_equals_the_single_gpu_ensemble(n_trials):
     world = 2
     cmd = [sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node', str(world),
            '--master-addr', '127.0.0.1', '--master-port', str(_free_port()),
-           os.path.join(ROOT, 'tools', 'check_peer_ensemble.py'), '20000']
+           os.path.join(ROOT, 'tools', 'check_peer_ensemble.py'), '20000', str(n_trials)]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
     assert r.returncode == 0 and 'PEER ENSEMBLE OK' in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]

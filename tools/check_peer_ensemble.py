@@ -26,7 +26,9 @@ def main():
     dev = torch.device('cuda', local)
     dist.init_process_group('nccl', device_id=dev)
     n_max = int(sys.argv[1]) if len(sys.argv) > 1 else 20000
-    W = 5 if world == 2 else 8                      # 5 trials on 2 ranks: uneven placement (3 + 2)
+    # default: 5 trials on 2 ranks (uneven placement, 3 + 2), else 8; argv[2] overrides (W = world: one trial
+    # per rank, the path whose hand-shake runs inside the trial kernel)
+    W = int(sys.argv[2]) if len(sys.argv) > 2 else (5 if world == 2 else 8)
     dead = synth.dead_mask(784)
     shapes = [(2, 128), (1, 36), (2, 77), (2, 128), (1, 128), (2, 64), (1, 2), (2, 100)]
     params = [synth.make_trial(t, 28, 1, *shapes[t], dead=dead, data_kind='fashion') for t in range(W)]
