@@ -319,8 +319,11 @@ def main():
 
     def step(i):
         if peer is not None:
-            # fused kernel + kernel 3 fused with the collective over NVLink peer memory: one C call
-            last[0] = peer.step(xs[i % len(xs)])
+            # one native call and (one trial per GPU) ONE kernel per rank and step: partial means go straight
+            # into the owners' slots over NVLink, the cross-rank sum of batch i rides in the kernel of batch i + 1
+            prev = peer.step_pipelined(xs[i % len(xs)])
+            if prev is not None:
+                last[0] = prev
         elif reducer is not None:
             last[0] = dens.forward_peer(xs[i % len(xs)], reducer)
         elif dens is not None:
@@ -335,6 +338,10 @@ def main():
             last[0] = ens.forward(xs[i % len(xs)], out=out)
 
     def drain():
+        if peer is not None:
+            res = peer.flush()          # completes the last batch (stand-alone sum of its slots)
+            if res is not None:
+                last[0] = res
         for k in range(2):
             if pending[k] is not None:
                 pending[k].wait()

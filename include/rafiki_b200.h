@@ -226,6 +226,21 @@ int rfk_peer_allgather_u8(rfk_peer_t* p, int64_t n, const uint8_t** gathered, vo
 int rfk_peer_ensemble_step(rfk_peer_t* p, rfk_mlp_t* const* trials, int w, int total_trials,
                            const uint8_t* x, int64_t n, void* workspace, size_t workspace_bytes,
                            float** result, void* stream);
+/*
+ * Pipelined form of the same step for back-to-back batches (a serving loop): with one trial per GPU
+ * the cross-rank sum of batch s is carried inside the trial kernel of batch s + 1 (an idle warp of
+ * every CTA adds this GPU's share of the rows while the tensor cores work on the new batch), so a
+ * step is ONE kernel per rank and no communication kernel stands between two trial kernels.
+ * *prev_result is the result buffer of the PREVIOUS call's batch (NULL after the first call); on the
+ * root it is complete once `stream` has passed this call.  rfk_peer_flush completes the last batch
+ * and returns its buffer.  Other configurations run rfk_peer_ensemble_step underneath and hand each
+ * result out one call later, so a caller sees one behaviour.  Replaces the same reference code as
+ * rfk_peer_ensemble_step.
+ */
+int rfk_peer_ensemble_step_pipelined(rfk_peer_t* p, rfk_mlp_t* const* trials, int w, int total_trials,
+                                     const uint8_t* x, int64_t n, void* workspace,
+                                     size_t workspace_bytes, float** prev_result, void* stream);
+int rfk_peer_flush(rfk_peer_t* p, float** result, void* stream);
 
 #ifdef __cplusplus
 }

@@ -66,6 +66,8 @@ PROTOTYPES = {
     'rfk_peer_upload_slot': (_i, [_vp, _i64, _c.POINTER(_vp), _c.POINTER(_i64), _c.POINTER(_i64)]),
     'rfk_peer_allgather_u8': (_i, [_vp, _i64, _c.POINTER(_vp), _vp]),
     'rfk_peer_ensemble_step': (_i, [_vp, _c.POINTER(_vp), _i, _i, _vp, _i64, _vp, _sz, _c.POINTER(_vp), _vp]),
+    'rfk_peer_ensemble_step_pipelined': (_i, [_vp, _c.POINTER(_vp), _i, _i, _vp, _i64, _vp, _sz, _c.POINTER(_vp), _vp]),
+    'rfk_peer_flush': (_i, [_vp, _c.POINTER(_vp), _vp]),
 }
 
 

@@ -25,6 +25,7 @@
 #include <stdlib.h>
 
 #include <atomic>
+#include <type_traits>
 
 #include "fused_common.cuh"
 #include "pack.cuh"
@@ -63,7 +64,7 @@ constexpr int kThreads = (kEpiWarps + kConvWarps + 4) * 32;   // 640
 constexpr int WARP_LOAD = kEpiWarps + kConvWarps, WARP_MMA = WARP_LOAD + 1, WARP_FWD = WARP_LOAD + 2,
               WARP_TAIL = WARP_LOAD + 3;
 constexpr int kRegsLaunch = 96;
-constexpr int kRegsEpi = 136, kRegsConv = 72, kRegsLight = 56;
+constexpr int kRegsEpi = 136, kRegsConv = 72, kRegsLight = 64;
 // setmaxnreg.inc only hands out what the CTA's own warps have given back (the launch allocation)
 static_assert(kEpiWarps * kRegsEpi + kConvWarps * kRegsConv + 4 * kRegsLight <= (kEpiWarps + kConvWarps + 4) * kRegsLaunch,
               "setmaxnreg budget exceeds the launch allocation");
@@ -268,18 +269,16 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
           for (int j = 0; j < CPAD; ++j) sts_f32_if(dst + 4u * j, __fdiv_rn(z[j] * inv, P.div_f), j < C);
         }
         if (!may_store) {
-          if (lane == 0) {
+          if (lane < P.hook.n_wait) {                 // one flag word per lane: the polls overlap
             const long long t0 = clock64();
-            for (int q = 0; q < P.hook.n_wait; ++q) {
-              unsigned int v;
-              do {
-                asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(P.hook.wait_flags + q) : "memory");
-                if (clock64() - t0 > 4000000000LL) {
-                  printf("rafiki_b200: pair kernel timed out waiting for its output slot (block %d)\n", blockIdx.x);
-                  __trap();
-                }
-              } while ((int)(v - P.hook.wait_value) < 0);
-            }
+            unsigned int v;
+            do {
+              asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(P.hook.wait_flags + lane) : "memory");
+              if (clock64() - t0 > 4000000000LL) {
+                printf("rafiki_b200: pair kernel timed out waiting for its output slot (block %d)\n", blockIdx.x);
+                __trap();
+              }
+            } while ((int)(v - P.hook.wait_value) < 0);
           }
           __syncwarp();
           may_store = true;
@@ -511,35 +510,49 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
       const long long per = (span + gridDim.x - 1) / gridDim.x;
       const long long lo = P.hook.carry_v_lo + per * blockIdx.x;
       const long long hi = lo + per < P.hook.carry_v_hi ? lo + per : P.hook.carry_v_hi;
-      for (long long i = lo + lane; i < hi; i += 32) {
-        double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
-        for (int j0 = 0; j0 < G; j0 += 4) {          // four slots in flight (the warp has 56 registers)
-          float4 v[4];
+      // Eight 16-byte loads in flight per lane (kPos positions x up to kSlots slots per round): the loop is bound
+      // by memory latency (the slots were written by peers, the trial kernel keeps L2 busy), not by the adds
+      auto carry_loop = [&](auto kPosTag, auto kSlotsTag) {
+        constexpr int kPos = decltype(kPosTag)::value, kSlots = decltype(kSlotsTag)::value;
+        for (long long i = lo + lane; i < hi; i += 32 * kPos) {
+          double acc[kPos][4];
 #pragma unroll
-          for (int u = 0; u < 4; ++u)
-            if (j0 + u < G) v[u] = __ldcg(reinterpret_cast<const float4*>(P.hook.carry_slot[j0 + u]) + i);
+          for (int u = 0; u < kPos; ++u) acc[u][0] = acc[u][1] = acc[u][2] = acc[u][3] = 0.0;
+          for (int j0 = 0; j0 < G; j0 += kSlots) {
+            float4 v[kPos][kSlots];
 #pragma unroll
-          for (int u = 0; u < 4; ++u)
-            if (j0 + u < G) {
-              s0 += (double)v[u].x; s1 += (double)v[u].y; s2 += (double)v[u].z; s3 += (double)v[u].w;
+            for (int q = 0; q < kSlots; ++q)
+              if (j0 + q < G) {
+                const float4* sl = reinterpret_cast<const float4*>(P.hook.carry_slot[j0 + q]);
+#pragma unroll
+                for (int u = 0; u < kPos; ++u)
+                  if (i + 32 * u < hi) v[u][q] = __ldcg(sl + i + 32 * u);
+              }
+#pragma unroll
+            for (int q = 0; q < kSlots; ++q)
+              if (j0 + q < G) {
+#pragma unroll
+                for (int u = 0; u < kPos; ++u)
+                  if (i + 32 * u < hi) {
+                    acc[u][0] += (double)v[u][q].x; acc[u][1] += (double)v[u][q].y;
+                    acc[u][2] += (double)v[u][q].z; acc[u][3] += (double)v[u][q].w;
+                  }
+              }
+          }
+#pragma unroll
+          for (int u = 0; u < kPos; ++u)
+            if (i + 32 * u < hi) {
+              float4 o;
+              o.x = (float)acc[u][0]; o.y = (float)acc[u][1]; o.z = (float)acc[u][2]; o.w = (float)acc[u][3];
+              reinterpret_cast<float4*>(P.hook.carry_out)[i + 32 * u] = o;
             }
         }
-        float4 o;
-        o.x = (float)s0; o.y = (float)s1; o.z = (float)s2; o.w = (float)s3;
-        reinterpret_cast<float4*>(P.hook.carry_out)[i] = o;
-      }
-      __syncwarp();
-      if (lane == 0) {
-        __threadfence_system();
-        if (atomicAdd(P.hook.carry_counter, 1u) == gridDim.x - 1) {      // last CTA: all my rows are in place
-          atomicExch(P.hook.carry_counter, 0u);
-          __threadfence_system();
-          asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(P.hook.carry_done), "r"(P.hook.carry_step) : "memory");
-          for (int j = 0; j < G; ++j)
-            asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(P.hook.carry_consumed[j]), "r"(P.hook.carry_step)
-                         : "memory");
-        }
-      }
+      };
+      if (G <= 2)
+        carry_loop(std::integral_constant<int, 4>{}, std::integral_constant<int, 2>{});
+      else
+        carry_loop(std::integral_constant<int, 2>{}, std::integral_constant<int, 4>{});
+      __syncwarp();      // the sums are published at the end of the kernel, with the output hand-shake
     }
   } else if (warp == WARP_MMA && leader) {
     // =============================================================== layer-1 MMA issuer (leader CTA, for the pair)
@@ -623,13 +636,21 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
   cluster_sync_all();            // neither CTA leaves (or frees tensor memory) while the other may still signal it
   if (warp == WARP_MMA) tmem_dealloc_pair<TMEM_COLS>(tmem_base);
   if (P.hook.n_signal > 0 && threadIdx.x == 0) {
-    // every output store of this CTA precedes the cluster barrier above; the last CTA out publishes the step
+    // Every store of this CTA (its tiles' outputs, its share of the carried sums) precedes the cluster barrier
+    // above.  ONE system-scope fence per CTA, then the last CTA out publishes the flags with plain stores: a
+    // release store per flag would pay a system-wide memory barrier (~1.5 us) each.
     __threadfence_system();
     if (atomicAdd(P.hook.counter, 1u) == gridDim.x - 1) {
       atomicExch(P.hook.counter, 0u);
-      __threadfence_system();
+      __threadfence();
       for (int q = 0; q < P.hook.n_signal; ++q)
-        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(P.hook.signal_flags[q]), "r"(P.hook.signal_value) : "memory");
+        asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(P.hook.signal_flags[q]), "r"(P.hook.signal_value) : "memory");
+      if (P.hook.n_carry > 0) {
+        asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(P.hook.carry_done), "r"(P.hook.carry_step) : "memory");
+        for (int j = 0; j < P.hook.n_carry; ++j)
+          asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(P.hook.carry_consumed[j]), "r"(P.hook.carry_step)
+                       : "memory");
+      }
     }
   }
 }

@@ -37,6 +37,11 @@ struct PeerPtrs {
   unsigned int* flags[kMaxRanks];    // flag block of every rank (peer mapped): [0,G) ready, [G,2G) done, [2G] counter
 };
 
+// plain system-scope store: for flag stores that follow ONE __threadfence_system() (a release store each
+// would pay a system-wide memory barrier per flag)
+__device__ __forceinline__ void st_relaxed_sys(unsigned int* p, unsigned int v) {
+  asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
 __device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
@@ -242,14 +247,14 @@ extern "C" int rfk_peer_wait(const unsigned int* flags_of_this_rank, int world, 
 // every rank, the layout and the step counters, so that one C call enqueues a whole step:
 //   [all-gather of the uint8 query slices over NVLink]  ->  fused trial kernel  ->  cross-rank mean.
 // Block layout (the same on every rank, so each rank can compute every peer's addresses):
-//   partial[2] | result[2] | queries[2] | slots[2][world] | flags
+//   partial[2] | result[2] | queries[2] | slots[3][world] | flags
 // where partial / result hold max_n * n_classes floats, queries max_n * d bytes, all rounded up to
 // 256 bytes, `slots` (2 x world buffers: where each rank's kernel stores its partial means on the root)
 // and the flag words listed in peer_layout().
 namespace {
 
 struct PeerLayout {
-  size_t buf_bytes, x_bytes, off_partial[2], off_result[2], off_x[2], off_slots[2], off_flags, total;
+  size_t buf_bytes, x_bytes, off_partial[2], off_result[2], off_x[2], off_slots[3], off_flags, total;
   int f_arrived, f_consumed, f_counter, f_sumcounter, f_done;    // indices into the flag words (see below)
 };
 
@@ -261,7 +266,9 @@ PeerLayout peer_layout(int world, int64_t max_n, int d, int n_classes) {
   for (int k = 0; k < 2; ++k) { L.off_partial[k] = off; off += L.buf_bytes; }
   for (int k = 0; k < 2; ++k) { L.off_result[k] = off; off += L.buf_bytes; }
   for (int k = 0; k < 2; ++k) { L.off_x[k] = off; off += L.x_bytes; }
-  for (int k = 0; k < 2; ++k) { L.off_slots[k] = off; off += (size_t)world * L.buf_bytes; }   // one slot per rank (used on the root)
+  // one slot per source rank, three deep in the scatter form: the kernel of step s overwrites what step s - 3
+  // left, which its owner consumed a whole kernel ago, so no rank ever waits for a slower one to free a slot
+  for (int k = 0; k < 3; ++k) { L.off_slots[k] = off; off += (size_t)world * L.buf_bytes; }
   L.off_flags = off;
   // flag words: [0,G) partials ready | [G,2G) slice in place | [2G] block counter | [2G+1,3G+1) query slice ready |
   //             [3G+1,4G+1) rank's partial means have arrived in its slot (on every owner) | [4G+1,5G+1) owner j has
@@ -368,8 +375,8 @@ peer_gather_sum_kernel(const SlotPtrs ptrs, const unsigned int* arrived, int wor
     if (atomicAdd(counter, 1u) == gridDim.x - 1) {     // last block: every slot has been read, every row stored
       atomicExch(counter, 0u);
       __threadfence_system();
-      if (done_flag != nullptr) st_release_sys(done_flag, step);
-      for (int j = 0; j < world; ++j) st_release_sys(ptrs.consumed[j], step);
+      if (done_flag != nullptr) st_relaxed_sys(done_flag, step);
+      for (int j = 0; j < world; ++j) st_relaxed_sys(ptrs.consumed[j], step);
     }
   }
 }
@@ -383,6 +390,11 @@ struct rfk_peer {
   uint8_t* base[kMaxRanks] = {nullptr};
   unsigned int rstep = 0, gstep = 0;       // reduce / gather steps issued so far (the same on every rank)
   int grid_blocks = 0;
+  // pipelined steps: the step whose slots have not been summed yet (0: none) and its batch size; the result
+  // of the newest finished step for callers of the pipelined form
+  unsigned int pending_step = 0;
+  int64_t pending_n = 0;
+  float* held_result = nullptr;
 };
 
 extern "C" int rfk_peer_block_bytes(int world, int64_t max_n, int d, int n_classes, size_t* out) {
@@ -465,6 +477,109 @@ extern "C" int rfk_peer_allgather_u8(rfk_peer_t* p, int64_t n, const uint8_t** g
   return RFK_OK;
 }
 
+namespace {
+
+// rows (in pair tiles of 256) that rank j owns in the scatter form
+inline void owner_bounds(int64_t n, int G, int* bound) {
+  const int n_pt = (int)((n + 255) / 256);
+  for (int j = 0; j < G; ++j) bound[j] = (int)((long long)n_pt * j / G);
+  bound[G] = n_pt;
+}
+
+// Scatter form, trial kernel of step `step`: every tile's partial means go to the owner of its rows.  With
+// carry_step != 0 the kernel also carries the reduction of that earlier step (batch carry_n) in its idle warp.
+int scatter_launch(rfk_peer* p, rfk_mlp_t* const* trials, int total_trials, const uint8_t* x, int64_t n, void* workspace,
+                   size_t workspace_bytes, unsigned int step, unsigned int carry_step, int64_t carry_n, void* stream) {
+  const int G = p->world, k = (int)(step % 3);
+  unsigned int* my_flags = reinterpret_cast<unsigned int*>(p->base[p->rank] + p->L.off_flags);
+  unsigned int* root_flags = reinterpret_cast<unsigned int*>(p->base[p->root] + p->L.off_flags);
+  rfk::PeerHook hook;
+  memset(&hook, 0, sizeof(hook));
+  hook.wait_value = step >= 3 ? step - 3 : 0;
+  hook.signal_value = step;
+  hook.counter = my_flags + p->L.f_counter;
+  hook.wait_flags = my_flags + p->L.f_consumed;          // one word per owner
+  hook.n_wait = G;
+  hook.n_signal = G;
+  hook.n_owner = G;
+  owner_bounds(n, G, hook.owner_bound);
+  for (int j = 0; j < G; ++j) {
+    hook.signal_flags[j] = reinterpret_cast<unsigned int*>(p->base[j] + p->L.off_flags) + p->L.f_arrived + p->rank;
+    hook.out_owner[j] = reinterpret_cast<float*>(p->base[j] + p->L.off_slots[k] + (size_t)p->rank * p->L.buf_bytes);
+  }
+  if (carry_step != 0) {
+    const int kp = (int)(carry_step % 3), kr = (int)(carry_step & 1);
+    int bound[kMaxRanks + 1];
+    owner_bounds(carry_n, G, bound);
+    const long long row_lo = (long long)bound[p->rank] * 256, row_hi_ = (long long)bound[p->rank + 1] * 256;
+    const long long row_hi = row_hi_ < carry_n ? row_hi_ : carry_n;
+    hook.n_carry = G;
+    hook.carry_step = carry_step;
+    hook.carry_v_lo = row_lo * p->n_classes / 4;
+    hook.carry_v_hi = (row_hi > row_lo ? row_hi : row_lo) * p->n_classes / 4;
+    hook.carry_arrived = my_flags + p->L.f_arrived;
+    hook.carry_done = root_flags + p->L.f_done + p->rank;
+    hook.carry_counter = my_flags + p->L.f_sumcounter;
+    hook.carry_out = reinterpret_cast<float*>(p->base[p->root] + p->L.off_result[kr]);
+    for (int j = 0; j < G; ++j) {
+      hook.carry_slot[j] = reinterpret_cast<const float*>(p->base[p->rank] + p->L.off_slots[kp] + (size_t)j * p->L.buf_bytes);
+      hook.carry_consumed[j] = reinterpret_cast<unsigned int*>(p->base[j] + p->L.off_flags) + p->L.f_consumed + p->rank;
+    }
+  }
+  {   // development switches (timing only, results become wrong): RFK_PEER_DEBUG bits 2 no carry, 4 local output, 8 no hand-shake, 16 empty carry
+    static const int dbg = []() { const char* e = getenv("RFK_PEER_DEBUG"); return e ? atoi(e) : 0; }();
+    if (dbg & 2) hook.n_carry = 0;
+    if (dbg & 4) hook.n_owner = 0;
+    if (dbg & 8) hook.n_wait = hook.n_signal = 0;
+    if (dbg & 16) hook.carry_v_hi = hook.carry_v_lo;      // hand-shake of the carried reduction without its loads and stores
+  }
+  rfk::set_peer_hook(&hook);
+  const int rc = rfk_ensemble_forward(trials, 1, total_trials, x, n, hook.out_owner[p->rank], workspace, workspace_bytes, stream);
+  if (rfk::peer_hook_pending()) {      // the call did not reach the pair kernel after all
+    rfk::set_peer_hook(nullptr);
+    rfk::set_error("peer_ensemble_step: internal routing error (hook not consumed)");
+    return RFK_ERR_INVALID;
+  }
+  return rc;
+}
+
+// Scatter form, stand-alone reduction of step `step`: my rows of the G slots -> the root's result; the root then
+// waits for every rank's rows.
+int scatter_sum(rfk_peer* p, unsigned int step, int64_t n, void* stream) {
+  const int G = p->world, k = (int)(step % 3), kr = (int)(step & 1);
+  unsigned int* my_flags = reinterpret_cast<unsigned int*>(p->base[p->rank] + p->L.off_flags);
+  unsigned int* root_flags = reinterpret_cast<unsigned int*>(p->base[p->root] + p->L.off_flags);
+  int bound[kMaxRanks + 1];
+  owner_bounds(n, G, bound);
+  const long long row_lo = (long long)bound[p->rank] * 256, row_hi_ = (long long)bound[p->rank + 1] * 256;
+  const long long row_hi = row_hi_ < n ? row_hi_ : n;
+  SlotPtrs sp;
+  for (int j = 0; j < kMaxRanks; ++j) {
+    sp.slot[j] = nullptr;
+    sp.consumed[j] = nullptr;
+    if (j < G) {
+      sp.slot[j] = reinterpret_cast<const float*>(p->base[p->rank] + p->L.off_slots[k] + (size_t)j * p->L.buf_bytes);
+      sp.consumed[j] = reinterpret_cast<unsigned int*>(p->base[j] + p->L.off_flags) + p->L.f_consumed + p->rank;
+    }
+  }
+  float* res = reinterpret_cast<float*>(p->base[p->root] + p->L.off_result[kr]);
+  const long long v_lo = row_lo * p->n_classes / 4, v_hi = (row_hi > row_lo ? row_hi : row_lo) * p->n_classes / 4;
+  const long long want = (v_hi - v_lo + kThreads - 1) / kThreads;
+  const int grid = (int)(want < 1 ? 1 : (want < (long long)p->grid_blocks ? want : (long long)p->grid_blocks));
+  peer_gather_sum_kernel<<<grid, kThreads, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      sp, my_flags + p->L.f_arrived, G, step, v_lo, v_hi, res, my_flags + p->L.f_sumcounter, root_flags + p->L.f_done + p->rank);
+  RFK_LAUNCH_CHECK("peer_gather_sum_kernel");
+  if (p->rank == p->root) return rfk_peer_wait_flags(root_flags + p->L.f_done, G, step, stream);
+  return RFK_OK;
+}
+
+bool scatter_capable(const rfk_peer* p, rfk_mlp_t* const* trials, int w, int total_trials, int64_t n) {
+  return w == 1 && total_trials == p->world && p->world > 1 && trials != nullptr && trials[0]->fusable &&
+         trials[0]->dtype != RFK_F32 && rfk::pair_applicable(trials[0]->d, n);
+}
+
+}  // namespace
+
 extern "C" int rfk_peer_ensemble_step(rfk_peer_t* p, rfk_mlp_t* const* trials, int w, int total_trials,
                                       const uint8_t* x, int64_t n, void* workspace, size_t workspace_bytes,
                                       float** result, void* stream) {
@@ -473,6 +588,11 @@ extern "C" int rfk_peer_ensemble_step(rfk_peer_t* p, rfk_mlp_t* const* trials, i
               "peer_ensemble_step: n %lld outside 1..%lld or n * classes not a multiple of 4", (long long)n,
               (long long)p->max_n);
   RFK_REQUIRE(x != nullptr, "peer_ensemble_step: x is NULL (pass the pointer rfk_peer_allgather_u8 returned)");
+  if (p->pending_step != 0) {          // a pipelined step is still open: finish it first
+    const int rc0 = scatter_sum(p, p->pending_step, p->pending_n, stream);
+    if (rc0 != RFK_OK) return rc0;
+    p->pending_step = 0;
+  }
   const unsigned int step = ++p->rstep;
   const int k = (int)(step & 1);
   const int64_t count = n * p->n_classes;
@@ -492,57 +612,13 @@ extern "C" int rfk_peer_ensemble_step(rfk_peer_t* p, rfk_mlp_t* const* trials, i
     unsigned int* my_flags = reinterpret_cast<unsigned int*>(p->base[p->rank] + p->L.off_flags);
     unsigned int* root_flags = reinterpret_cast<unsigned int*>(p->base[p->root] + p->L.off_flags);
     const int G = p->world;
-    const bool scatter = w == 1 && total_trials == G && G > 1 && trials != nullptr && trials[0]->fusable &&
-                         trials[0]->dtype != RFK_F32 && rfk::pair_applicable(trials[0]->d, n);
-    const int n_pt = (int)((n + 255) / 256);
-    rfk::PeerHook hook;
-    memset(&hook, 0, sizeof(hook));
-    hook.wait_value = step >= 2 ? step - 2 : 0;
-    hook.signal_value = step;
-    hook.counter = my_flags + p->L.f_counter;
+    const bool scatter = scatter_capable(p, trials, w, total_trials, n);
+    const unsigned int wait_value = step >= 2 ? step - 2 : 0;
     if (scatter) {
-      hook.wait_flags = my_flags + p->L.f_consumed;          // one word per owner
-      hook.n_wait = G;
-      hook.n_signal = G;
-      hook.n_owner = G;
-      for (int j = 0; j < G; ++j) {
-        hook.signal_flags[j] = reinterpret_cast<unsigned int*>(p->base[j] + p->L.off_flags) + p->L.f_arrived + p->rank;
-        hook.out_owner[j] = reinterpret_cast<float*>(p->base[j] + p->L.off_slots[k] + (size_t)p->rank * p->L.buf_bytes);
-        hook.owner_bound[j] = (int)((long long)n_pt * j / G);
-      }
-      hook.owner_bound[G] = n_pt;
-      rfk::set_peer_hook(&hook);
-      const int rc = rfk_ensemble_forward(trials, w, total_trials, x, n, hook.out_owner[p->rank], workspace, workspace_bytes,
-                                          stream);
-      if (rfk::peer_hook_pending()) {      // the call did not reach the pair kernel after all
-        rfk::set_peer_hook(nullptr);
-        rfk::set_error("peer_ensemble_step: internal routing error (hook not consumed)");
-        return RFK_ERR_INVALID;
-      }
+      int rc = scatter_launch(p, trials, total_trials, x, n, workspace, workspace_bytes, step, 0, 0, stream);
       if (rc != RFK_OK) return rc;
-      // my rows: add the G slots, store into the root's result, tell the root and free the slots
-      const long long row_lo = (long long)hook.owner_bound[p->rank] * 256, row_hi_ = (long long)hook.owner_bound[p->rank + 1] * 256;
-      const long long row_hi = row_hi_ < n ? row_hi_ : n;
-      SlotPtrs sp;
-      for (int j = 0; j < kMaxRanks; ++j) {
-        sp.slot[j] = nullptr;
-        sp.consumed[j] = nullptr;
-        if (j < G) {
-          sp.slot[j] = reinterpret_cast<const float*>(p->base[p->rank] + p->L.off_slots[k] + (size_t)j * p->L.buf_bytes);
-          sp.consumed[j] = reinterpret_cast<unsigned int*>(p->base[j] + p->L.off_flags) + p->L.f_consumed + p->rank;
-        }
-      }
-      float* res = reinterpret_cast<float*>(p->base[p->root] + p->L.off_result[k]);
-      const long long v_lo = row_lo * p->n_classes / 4, v_hi = (row_hi > row_lo ? row_hi : row_lo) * p->n_classes / 4;
-      const long long want = (v_hi - v_lo + kThreads - 1) / kThreads;
-      const int grid = (int)(want < 1 ? 1 : (want < (long long)p->grid_blocks ? want : (long long)p->grid_blocks));
-      peer_gather_sum_kernel<<<grid, kThreads, 0, st>>>(sp, my_flags + p->L.f_arrived, G, step, v_lo, v_hi, res,
-                                                        my_flags + p->L.f_sumcounter, root_flags + p->L.f_done + p->rank);
-      RFK_LAUNCH_CHECK("peer_gather_sum_kernel");
-      if (p->rank == p->root) {
-        const int rc2 = rfk_peer_wait_flags(root_flags + p->L.f_done, G, step, stream);
-        if (rc2 != RFK_OK) return rc2;
-      }
+      rc = scatter_sum(p, step, n, stream);
+      if (rc != RFK_OK) return rc;
       if (result != nullptr) *result = reinterpret_cast<float*>(p->base[p->rank] + p->L.off_result[k]);
       return RFK_OK;
     }
@@ -550,8 +626,8 @@ extern "C" int rfk_peer_ensemble_step(rfk_peer_t* p, rfk_mlp_t* const* trials, i
     float* slot = reinterpret_cast<float*>(p->base[p->root] + p->L.off_slots[k] + (size_t)p->rank * p->L.buf_bytes);
     const unsigned int* wait_flag = my_flags + p->L.f_consumed + p->root;
     unsigned int* signal_flag = root_flags + p->L.f_arrived + p->rank;
-    if (hook.wait_value > 0) {
-      const int rc = rfk_peer_wait_flags(wait_flag, 1, hook.wait_value, stream);
+    if (wait_value > 0) {
+      const int rc = rfk_peer_wait_flags(wait_flag, 1, wait_value, stream);
       if (rc != RFK_OK) return rc;
     }
     if (w > 0) {
@@ -610,5 +686,70 @@ extern "C" int rfk_peer_ensemble_step(rfk_peer_t* p, rfk_mlp_t* const* trials, i
     if (rc != RFK_OK) return rc;
   }
   if (result != nullptr) *result = reinterpret_cast<float*>(p->base[p->rank] + p->L.off_result[k]);
+  return RFK_OK;
+}
+
+
+// Pipelined form for back-to-back batches.  Same work as rfk_peer_ensemble_step, but in the scatter form the
+// reduction of step s rides inside the trial kernel of step s + 1 (an idle warp of every CTA adds this GPU's
+// rows while the tensor cores work), so a step is ONE kernel per rank.  *prev_result receives the result buffer
+// of the PREVIOUS step (NULL after the first call); on the root it is complete once `stream` has passed this
+// call.  rfk_peer_flush finishes the last step.  Configurations the scatter form does not take run the plain
+// step and hand its result out one call later, so callers see one behaviour.
+extern "C" int rfk_peer_ensemble_step_pipelined(rfk_peer_t* p, rfk_mlp_t* const* trials, int w, int total_trials,
+                                                const uint8_t* x, int64_t n, void* workspace, size_t workspace_bytes,
+                                                float** prev_result, void* stream) {
+  RFK_REQUIRE(p != nullptr, "peer_ensemble_step_pipelined: NULL argument");
+  static const bool reduce_mode = []() { const char* m = getenv("RFK_PEER_MODE"); return m != nullptr && m[0] == 'r'; }();
+  if (prev_result != nullptr) *prev_result = nullptr;
+  if (reduce_mode || !scatter_capable(p, trials, w, total_trials, n)) {
+    float* prev = p->held_result;
+    if (p->pending_step != 0) {
+      const int rc0 = rfk_peer_flush(p, &prev, stream);
+      if (rc0 != RFK_OK) return rc0;
+    }
+    float* cur = nullptr;
+    const int rc = rfk_peer_ensemble_step(p, trials, w, total_trials, x, n, workspace, workspace_bytes, &cur, stream);
+    if (rc != RFK_OK) return rc;
+    p->held_result = cur;
+    if (prev_result != nullptr) *prev_result = prev;
+    return RFK_OK;
+  }
+  RFK_REQUIRE(n >= 1 && n <= p->max_n && (n * p->n_classes) % 4 == 0,
+              "peer_ensemble_step_pipelined: n %lld outside 1..%lld or n * classes not a multiple of 4", (long long)n,
+              (long long)p->max_n);
+  RFK_REQUIRE(x != nullptr, "peer_ensemble_step_pipelined: x is NULL");
+  float* prev = p->held_result;
+  p->held_result = nullptr;
+  const unsigned int step = ++p->rstep;
+  const unsigned int carry = p->pending_step;
+  const int rc = scatter_launch(p, trials, total_trials, x, n, workspace, workspace_bytes, step, carry, p->pending_n, stream);
+  if (rc != RFK_OK) return rc;
+  if (carry != 0) {
+    static const int dbg = []() { const char* e = getenv("RFK_PEER_DEBUG"); return e ? atoi(e) : 0; }();
+    if (p->rank == p->root && !(dbg & 1)) {      // every rank's rows of the carried step are in place before the caller reads them
+      unsigned int* root_flags = reinterpret_cast<unsigned int*>(p->base[p->root] + p->L.off_flags);
+      const int rc2 = rfk_peer_wait_flags(root_flags + p->L.f_done, p->world, carry, stream);
+      if (rc2 != RFK_OK) return rc2;
+    }
+    prev = reinterpret_cast<float*>(p->base[p->rank] + p->L.off_result[carry & 1]);
+  }
+  p->pending_step = step;
+  p->pending_n = n;
+  if (prev_result != nullptr) *prev_result = prev;
+  return RFK_OK;
+}
+
+extern "C" int rfk_peer_flush(rfk_peer_t* p, float** result, void* stream) {
+  RFK_REQUIRE(p != nullptr, "peer_flush: NULL argument");
+  float* res = p->held_result;
+  p->held_result = nullptr;
+  if (p->pending_step != 0) {
+    const int rc = scatter_sum(p, p->pending_step, p->pending_n, stream);
+    if (rc != RFK_OK) return rc;
+    res = reinterpret_cast<float*>(p->base[p->rank] + p->L.off_result[p->pending_step & 1]);
+    p->pending_step = 0;
+  }
+  if (result != nullptr) *result = res;
   return RFK_OK;
 }

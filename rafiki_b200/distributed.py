@@ -273,6 +273,8 @@ class PeerEnsemble:
             from .engine import Workspace
             self._ws = Workspace(self.device)
         self._plans = {}
+        self._views = {}
+        self._last_n = None
         self._res = ctypes.c_void_p()
         dist.barrier(group=group)
 
@@ -307,6 +309,43 @@ class PeerEnsemble:
         stream = ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
         self._check(self._lib.rfk_peer_allgather_u8(self._ctx, n, ctypes.byref(out), stream))
         return self._as_tensor(out.value, (n, self.d), '|u1', torch.uint8)
+
+    def step_pipelined(self, x):
+        """Back-to-back batches (``rfk_peer_ensemble_step_pipelined``): enqueues this batch and returns the
+        result tensor of the PREVIOUS call's batch (``None`` after the first call); with one trial per GPU
+        the cross-rank sum of a batch rides inside the next batch's trial kernel.  ``flush()`` completes
+        and returns the last one."""
+        n = x.shape[0]
+        plan = self._plans.get(n)
+        if plan is None:
+            ws, ws_bytes = (ctypes.c_void_p(0), 0)
+            if self.local is not None:
+                ws, ws_bytes = self._ws.get(self.local.workspace_bytes(n))
+            plan = self._plans[n] = [ws, ws_bytes, {}]
+        ws, ws_bytes, views = plan
+        res = self._res
+        rc = self._lib.rfk_peer_ensemble_step_pipelined(
+            self._ctx, self._handles, self._w, self.n_trials, x.data_ptr(), n, ws, ws_bytes, ctypes.byref(res),
+            ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream))
+        if rc != 0:
+            self._check(rc)
+        prev_n, self._last_n = self._last_n, n
+        return self._view(res.value, prev_n)
+
+    def flush(self):
+        res = ctypes.c_void_p()
+        self._check(self._lib.rfk_peer_flush(self._ctx, ctypes.byref(res),
+                                             ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)))
+        n, self._last_n = self._last_n, None
+        return self._view(res.value, n)
+
+    def _view(self, ptr, n):
+        if not ptr or n is None:
+            return None
+        out = self._views.get((ptr, n))
+        if out is None:
+            out = self._views[(ptr, n)] = self._as_tensor(ptr, (n, self.n_classes))
+        return out
 
     def step(self, x):
         """One serving step on the current stream.  The host side is kept to one native call: scratch

@@ -63,6 +63,23 @@ def main():
                 stepno, n, 'identical' if int(flag.item()) == 0 else 'DIFFERS', e_gpu, e_or), flush=True)
             ok = ok and int(flag.item()) == 0 and e_gpu <= 1e-6 and e_or <= 2e-3
         dist.barrier()
+    # the pipelined form: the result of a batch comes back one call later (or from flush)
+    batches = [synth.make_queries(n_max - 2 * i, 28, 1, 'fashion', seed=60 + i, dead=dead).reshape(-1, 784) for i in range(5)]
+    got = []
+    for X in batches:
+        prev = peer.step_pipelined(torch.from_numpy(X).to(dev))
+        if prev is not None:
+            got.append(prev.clone())
+    got.append(peer.flush().clone())
+    torch.cuda.synchronize()
+    if rank == 0:
+        for i, X in enumerate(batches):
+            want = full.forward(torch.from_numpy(X).to(dev))
+            e = float((got[i].double() - want.double()).abs().max().item())
+            worst = max(worst, e)
+            print('pipelined batch %d n %6d: vs single GPU %.3e' % (i, X.shape[0], e), flush=True)
+            ok = ok and e <= 1e-6 and got[i].shape == want.shape
+    dist.barrier()
     verdict = torch.tensor([1 if ok else 0], device=dev)
     dist.broadcast(verdict, 0)
     if rank == 0:

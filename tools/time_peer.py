@@ -42,8 +42,18 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return t[0].item(), t[1].item()
 
+    if os.environ.get('RFK_PEER_DEBUG'):
+        c = timed(lambda i: peer.step_pipelined(xs[i % 4]))
+        if rank == 0:
+            print('RFK_PEER_DEBUG=%s world %d: pipelined peer step %.1f us' % (os.environ['RFK_PEER_DEBUG'], world, c[0]), flush=True)
+        os._exit(0)
     a = timed(lambda i: ens.forward(xs[i % 4], out=out))
     b = timed(lambda i: peer.step(xs[i % 4]))
+    c = timed(lambda i: peer.step_pipelined(xs[i % 4]))
+    peer.flush()
+    torch.cuda.synchronize()
+    if rank == 0:
+        print('world %d: pipelined peer step %.1f us (host %.1f us per call)' % (world, c[0], c[1]), flush=True)
     if rank == 0:
         print('world %d: local fused forward %.1f us (host %.1f us per call); peer step %.1f us (host %.1f us per call)' % (
             world, a[0], a[1], b[0], b[1]), flush=True)
