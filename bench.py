@@ -10,7 +10,8 @@ Workloads (BASELINE.json `configs`):
   c3 (default)  8-trial TfFeedForward ensemble (D 784, H 128, L 2), batch 65536 -- the
                 configuration the north_star's targets are quoted on; it fits one GPU.  At N GPUs
                 the 8 trials are placed 8/N per GPU (one per GPU at N = 8), every GPU sees the whole
-                batch, and the partial means are summed onto rank 0 by an NCCL reduce: strong scaling.
+                batch, and the partial means are summed onto rank 0 through NVLink peer memory (the trial kernel
+                stores them into the owners' slots; rafiki_b200/csrc/peer.cu): strong scaling.
   c2            3-trial ensemble, batch 4096 per GPU; N > 1 runs independent replicas (weak scaling).
 
 `value` is device-resident throughput (queries already in HBM); `e2e` goes through the pinned-host
@@ -41,6 +42,8 @@ WORKLOADS = {
     'c4': dict(trials=1, batch=65536, image_size=32, channels=3, hidden=2048, layers=3, scaling='strong', shard='rows',
                name='wide MLP trial (3x2048 hidden), 32x32x3 queries, batch 65536 sharded data-parallel '
                     '(BASELINE configs[3])'),
+    'small': dict(trials=0, batch=262144, image_size=28, channels=1, hidden=0, layers=0, scaling='weak', small=True,
+                  name='memory-bound kernels alone (decode / NEAREST resize / ensemble mean) at a working set larger than L2'),
     'c5': dict(trials=3, batch=65536, image_size=28, channels=1, hidden=128, layers=2, scaling='weak', sweep=True,
                name='serving latency sweep, batch 1..65536, 3-trial ensemble (BASELINE configs[4])'),
 }
@@ -249,6 +252,62 @@ def run_latency_sweep(args, wl, ens, xs, out, params, rank):
     return 0
 
 
+def run_small_kernels(args, wl):
+    """Kernels 1 and 3 alone against the HBM roofline: achieved bytes/s of decode (-> bf16 / f32), the NEAREST
+    resize and the ensemble mean, inputs rotated over more than L2, CUDA events; one JSON line."""
+    import torch
+    from rafiki_b200 import engine
+    torch.cuda.set_device(0)
+    peaks = load_peaks()
+    peak = float(peaks.get('hbm_gbs', FALLBACK_PEAKS['hbm_gbs']))
+
+    def timed(fn, iters):
+        for i in range(max(args.warmup, 3)):
+            fn(i)
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for i in range(iters):
+            fn(i)
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / iters * 1e-3
+
+    iters = max(5, min(args.steps, 100))
+    n = wl['batch']
+    rows = []
+    xs = [torch.randint(0, 256, (n, 784), dtype=torch.uint8, device='cuda') for _ in range(2)]      # 2 x 205 MB
+    scale = torch.rand(784, device='cuda') + 0.5
+    shift = torch.randn(784, device='cuda')
+    for dt, sz in ((torch.bfloat16, 2), (torch.float32, 4)):
+        t = timed(lambda i: engine.decode_u8(xs[i & 1], scale, shift, out_dtype=dt), iters)
+        byts = n * 784 * (1 + sz)
+        rows.append({'kernel': 'decode_u8 -> %s' % str(dt).split('.')[-1], 'n': n, 'us': t * 1e6, 'algorithmic_bytes': byts,
+                     'gbs': byts / t / 1e9, 'frac': byts / t / 1e9 / peak})
+    x28 = [x.view(n, 28, 28) for x in xs]
+    t = timed(lambda i: engine.resize_decode_u8(x28[i & 1], 32), iters)
+    byts = n * (784 + 1024)
+    rows.append({'kernel': 'resize 28->32 (uint8)', 'n': n, 'us': t * 1e6, 'algorithmic_bytes': byts, 'gbs': byts / t / 1e9,
+                 'frac': byts / t / 1e9 / peak})
+    del xs, x28
+    for w, r in ((3, 4 * 1048576), (8, 2 * 1048576)):
+        sets = [[torch.rand(r, 10, device='cuda') for _ in range(w)] for _ in range(2)]
+        dst = torch.empty(r, 10, device='cuda')
+        t = timed(lambda i: engine.ensemble_mean(sets[i & 1], out=dst), iters)
+        byts = r * 10 * 4 * (w + 1)
+        rows.append({'kernel': 'ensemble_mean W=%d' % w, 'n': r, 'us': t * 1e6, 'algorithmic_bytes': byts, 'gbs': byts / t / 1e9,
+                     'frac': byts / t / 1e9 / peak})
+        del sets, dst
+    worst = min(rows, key=lambda k: k['frac'])
+    print(json.dumps({'metric': 'memory_bound_kernels_hbm_fraction', 'value': worst['frac'], 'unit': 'fraction of measured HBM copy bandwidth (worst kernel)',
+                      'n_gpus': 1, 'steps': iters, 'warmup': max(args.warmup, 3), 'higher_is_better': True, 'dtype': 'u8/f32',
+                      'data': 'synthetic', 'config': {'workload': wl['name']},
+                      'roofline': {'bound': 'hbm', 'achieved': worst['gbs'], 'peak': peak, 'unit': 'GB/s', 'frac': worst['frac'],
+                                   'traffic': None, 'kernel': worst['kernel'], 'peak_source': peaks['_source']},
+                      'kernels': rows}), flush=True)
+    return 0
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
@@ -258,12 +317,12 @@ def main():
     ap.add_argument('--workload', default='c3', choices=sorted(WORKLOADS))
     ap.add_argument('--compute', default='f16', choices=['f16', 'bf16', 'f32'])
     ap.add_argument('--no-cpu-baseline', action='store_true')
-    ap.add_argument('--reduce', default='peer', choices=['peer', 'gather', 'nccl'],
-                    help='N > 1, trial-per-GPU workloads: fused peer-memory reduce (default) or torch.distributed/NCCL')
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
     if args.impl == 'reference':
         return run_reference(args, wl)
+    if wl.get('small'):
+        return run_small_kernels(args, wl)
 
     import torch
     import torch.distributed as dist
@@ -296,7 +355,6 @@ def main():
     else:                              # independent replicas
         mine = list(range(W))
     from rafiki_b200 import _native
-    from rafiki_b200.distributed import DistributedEnsemble
     sampler = ClockSampler(local_rank)        # every rank, before the warm-up
     sampler.start()
     trials = [engine.Trial(params[t], compute=args.compute) for t in mine]
@@ -304,17 +362,11 @@ def main():
     xs = [torch.from_numpy(b).to(dev) for b in batches]
     out = torch.zeros((n, C), dtype=torch.float32, device=dev)
     do_reduce = world > 1 and wl['scaling'] == 'strong' and wl.get('shard') != 'rows'
-    dens = DistributedEnsemble(ens, W, C, dev, root=0) if do_reduce else None
-    reducer = peer = None
-    if do_reduce and args.reduce == 'peer':
+    peer = None
+    if do_reduce:
         from rafiki_b200.distributed import PeerEnsemble
         peer = PeerEnsemble(ens, W, n, d, C, dev, root=0)       # one native call per step
-    elif do_reduce and args.reduce == 'gather':
-        from rafiki_b200.distributed import PeerGather
-        reducer = PeerGather(n, C, dev, root=0)
 
-    outs = [out, torch.zeros_like(out)]
-    pending = [None, None]
     last = [None]
 
     def step(i):
@@ -324,16 +376,6 @@ def main():
             prev = peer.step_pipelined(xs[i % len(xs)])
             if prev is not None:
                 last[0] = prev
-        elif reducer is not None:
-            last[0] = dens.forward_peer(xs[i % len(xs)], reducer)
-        elif dens is not None:
-            # local fused kernel + NCCL reduce onto rank 0; two result buffers in turn, so the
-            # reduce of batch i overlaps the kernel of batch i+1
-            slot = i & 1
-            if pending[slot] is not None:
-                pending[slot].wait()
-            pending[slot] = dens.forward_async(xs[i % len(xs)], outs[slot])
-            last[0] = outs[slot]
         elif ens is not None:
             last[0] = ens.forward(xs[i % len(xs)], out=out)
 
@@ -342,10 +384,6 @@ def main():
             res = peer.flush()          # completes the last batch (stand-alone sum of its slots)
             if res is not None:
                 last[0] = res
-        for k in range(2):
-            if pending[k] is not None:
-                pending[k].wait()
-                pending[k] = None
 
     if wl.get('sweep'):
         sampler.stop()
@@ -478,30 +516,6 @@ def main():
                'note': 'each rank uploads only its 1/N of the rows from pinned host memory (own PCIe link, copy '
                        'stream), the slices are all-gathered over NVLink peer memory (rfk_peer_allgather_u8), '
                        'fused kernel, peer-memory reduce, rank 0 downloads the probabilities'}
-    elif dens is not None:
-        # every rank: pinned host batch -> device -> fused kernel -> reduce; rank 0: result -> pinned host
-        h_in = torch.from_numpy(batches[0]).pin_memory()
-        d_in = torch.empty_like(xs[0])
-        h_out = torch.empty((n, C), dtype=torch.float32).pin_memory()
-        e2e_steps = max(4, min(args.steps, 40))
-        for it in range(2 + e2e_steps):
-            if it == 2:
-                barrier()
-                t0 = time.perf_counter()
-            d_in.copy_(h_in, non_blocking=True)
-            res = dens.forward_peer(d_in, reducer) if reducer is not None else dens.forward(d_in, out=out)
-            if rank == 0:
-                h_out.copy_(res, non_blocking=True)
-        barrier()
-        dt = time.perf_counter() - t0
-        t = torch.tensor([dt], device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dt = float(t.item())
-        e2e = {'value': n * e2e_steps / dt, 'unit': 'queries/s', 'h2d_bytes_per_step': n * d * world,
-               'd2h_bytes_per_step': n * C * 4, 'steps': e2e_steps,
-               'note': 'every rank uploads the whole uint8 batch from pinned host memory (its own PCIe link), '
-                       'fused kernel, {}, rank 0 downloads the probabilities'.format(
-                           'gather fused into the trial kernel' if reducer is not None else 'NCCL reduce')}
     elif ens is not None:
         depth = 3
         pipe = engine.HostPipeline(ens, max_batch=n, depth=depth)
@@ -581,10 +595,8 @@ def main():
             except Exception:
                 traffic = None
         if do_reduce:
-            par = 'trial-per-gpu x{} + {}'.format(world, {
-                'peer': 'peer-memory reduce-scatter kernel, one native call per step (rfk_peer_ensemble_step)',
-                'gather': 'epilogue stores into the root over NVLink + sum',
-                'nccl': 'torch.distributed NCCL reduce'}[args.reduce])
+            par = ('trial-per-gpu x{}: partial means stored into peer memory over NVLink from the trial kernel, summed by '
+                   'their owners; one native call per step (rfk_peer_ensemble_step_pipelined)'.format(world))
         elif wl.get('shard') == 'rows':
             par = 'rows sharded x{}'.format(world)
         else:

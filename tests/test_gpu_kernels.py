@@ -442,7 +442,7 @@ def test_mixed_ensemble_with_an_external_plugin():
 
 def test_peer_reduce_single_rank_degenerates_to_a_rounded_copy():
     """The cross-GPU kernel with a world of one (the multi-rank case needs several GPUs and is
-    checked by tools/check_peer_reduce.py under torchrun): flags, step counters and the slice
+    checked by tests/test_gpu_multi.py under torchrun): flags, step counters and the slice
     arithmetic must work, and two steps in a row must reuse the flag block without a reset."""
     import ctypes
     lib = _native.load()
