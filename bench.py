@@ -160,8 +160,10 @@ def cpu_oracle_rate(params, batch, sample, repeats, threads):
     first `sample` queries of the batch."""
     from oracle import feedforward as ff     # the one place bench.py executes oracle/
     from threadpoolctl import threadpool_limits
-    side = int(round((batch.shape[1]) ** 0.5))
-    queries = batch[:sample].reshape(sample, side, side).tolist()
+    ch = int(params[0].get('channels', 1)) if isinstance(params[0], dict) else 1
+    side = int(round((batch.shape[1] // ch) ** 0.5))
+    shape = (sample, side, side) if ch == 1 else (sample, side, side, ch)
+    queries = batch[:sample].reshape(shape).tolist()
     times = []
     with threadpool_limits(limits=threads):
         for _ in range(repeats):
@@ -622,7 +624,7 @@ def main():
                          'traffic': traffic, 'traffic_source': traffic_source,
                          'kernel': ('gemm_bias_act_kernel x4 + decode (whole step; duration = timed region / steps)'
                                     if wl.get('shard') == 'rows' else
-                                    'fused_ensemble_kernel (one launch per step; duration = timed region / steps)'),
+                                    'fused_pair_kernel + ensemble_mean_vec4_kernel (whole step; duration = timed region / steps)'),
                          'peak_source': peaks['_source'] + ' (bf16 rates; same tensor rate for fp16)',
                          'flops_per_launch': flops_per_launch,
                          'hbm_gbs_algorithmic': n * (d + 4 * C) / (ms_launch * 1e-3) / 1e9},

@@ -63,28 +63,38 @@ class TfFeedForward(BaseModel):
 
     def predict_array(self, queries):
         """Binary fast path: list or ``uint8`` ndarray ``[n, S, S(, ch)]`` -> ``float32`` ndarray ``[n, C]``."""
-        return self.predict_tensor(self._queries_to_device(queries)).cpu().numpy()
+        if self._trial is None:
+            raise InvalidModelParamsException('model has no parameters loaded')
+        trial, x = self._queries_to_device(queries)
+        return trial.forward(x).cpu().numpy()
 
     def predict_tensor(self, x):
-        """Tensor fast path: ``uint8 [n, S, S(, ch)]`` CUDA tensor -> ``float32 [n, C]`` CUDA tensor."""
+        """Tensor fast path: ``uint8 [n, S, S(, ch)]`` CUDA tensor at the trial's ``image_size`` ->
+        ``float32 [n, C]`` CUDA tensor."""
         if self._trial is None:
             raise InvalidModelParamsException('model has no parameters loaded')
         return self._trial.forward(x)
 
     def _queries_to_device(self, queries):
-        """uint8 frames at their own size -> device -> Pillow-NEAREST resize ON THE GPU to the
-        trial's ``image_size`` (rafiki/model/dataset.py:76-78; the default knob is 32 for 28x28 queries)."""
+        """uint8 frames at their own size -> device.  Frames that are not the trial's ``image_size`` (the
+        default knob is 32 for 28x28 queries; rafiki/model/dataset.py:76-78 resizes with Pillow NEAREST):
+        tensor-core trials fold that resize into their first layer and read the frames as they are; the
+        fp32 path resizes on the GPU (``rfk_resize_decode_u8``).  Returns (trial to run, device tensor)."""
         import torch
         from rafiki_b200 import engine
         from rafiki_b200.model.dataset import queries_to_uint8
         im_sz = self._image_size()
         frames = np.ascontiguousarray(queries_to_uint8(queries))
         x = torch.from_numpy(frames).cuda()
+        trial = self._trial
         if frames.ndim >= 3 and (frames.shape[1] != im_sz or frames.shape[2] != im_sz):
             if frames.shape[1] != frames.shape[2]:
                 raise ValueError('queries must be square images, got {}'.format(frames.shape[1:]))
-            x = engine.resize_decode_u8(x, im_sz)
-        return x
+            if self._compute in ('f32', 'fp32'):
+                x = engine.resize_decode_u8(x, im_sz)
+            else:
+                trial = self._trial.for_input(frames.shape[1])
+        return trial, x
 
     def _image_size(self):
         im_sz = self._knobs.get('image_size')

@@ -78,6 +78,44 @@ class Workspace:
 _Workspace = Workspace
 
 
+def fold_resize_into_params(params, s_in, channels=1):
+    """Parameters of a trial trained on ``S x S`` images -> equivalent parameters that take the
+    ``s_in x s_in`` frames the queries arrive in (rafiki/model/dataset.py:76-78 resizes 28 x 28 queries to
+    the ``image_size`` knob, 32 by default, before the network sees them).
+
+    Pillow's NEAREST resize is a gather, and BatchNormalization + the first Dense layer are affine in the
+    resized pixels, so both fold into the first layer: ``K'[src] = sum over dst with source src of
+    inv[dst] * K[dst]`` and ``b' = b + shift @ K`` (float64 on the host, once).  The kernels then read the
+    raw frames: no resize pass over the batch, and a shorter contraction (784 instead of 1024).
+    """
+    from .model.dataset import nearest_index_table
+    S = int(params['image_size'])
+    ch = int(channels)
+    rows = nearest_index_table(s_in, S)
+    cols = nearest_index_table(s_in, S)
+    src = ((rows[:, None] * s_in + cols[None, :])[:, :, None] * ch + np.arange(ch)[None, None, :]).reshape(-1)
+    eps = float(params.get('bn_eps', 1e-3))
+    g, b, m, v = (np.asarray(params[k], np.float64) for k in ('bn_gamma', 'bn_beta', 'bn_mean', 'bn_var'))
+    inv = g / np.sqrt(v + eps)
+    shift = b - m * inv
+    K = np.asarray(params['kernels'][0], np.float64)
+    if K.shape[0] != S * S * ch:
+        raise ValueError('first kernel has {} rows, expected {}'.format(K.shape[0], S * S * ch))
+    d_in = s_in * s_in * ch
+    K_eff = np.zeros((d_in, K.shape[1]), np.float64)
+    np.add.at(K_eff, src, K * inv[:, None])
+    out = dict(params)
+    out['kernels'] = [K_eff.astype(np.float32)] + [np.asarray(k, np.float32) for k in params['kernels'][1:]]
+    out['biases'] = [(np.asarray(params['biases'][0], np.float64) + shift @ K).astype(np.float32)] + \
+        [np.asarray(x, np.float32) for x in params['biases'][1:]]
+    out['bn_gamma'] = np.ones(d_in, np.float32)                 # identity BatchNormalization: inv = 1, shift = 0
+    out['bn_beta'] = np.zeros(d_in, np.float32)
+    out['bn_mean'] = np.zeros(d_in, np.float32)
+    out['bn_var'] = np.full(d_in, 1.0 - eps, np.float32)
+    out['image_size'] = int(s_in)
+    return out
+
+
 class Trial:
     """One packed trial (TfFeedForward network) on one GPU."""
 
@@ -100,6 +138,23 @@ class Trial:
                                     if s * s * ch == self.d), None)
         self.channels = self.d // (self.image_size ** 2) if self.image_size else 1
         self._ws = Workspace(self.device)
+        self._params = params
+        self._folded = {}
+
+    def for_input(self, s_in):
+        """The same trial packed for ``s_in x s_in`` frames (the resize folded into its first layer, see
+        :func:`fold_resize_into_params`); tensor-core modes only -- the fp32 parity path keeps the explicit
+        resize kernel so that its arithmetic stays the oracle's, operation for operation."""
+        s_in = int(s_in)
+        if s_in == self.image_size:
+            return self
+        if self.compute in ('f32', 'fp32'):
+            raise ValueError('the fp32 path does not fold the resize')
+        t = self._folded.get(s_in)
+        if t is None:
+            t = self._folded[s_in] = Trial(fold_resize_into_params(self._params, s_in, self.channels),
+                                           compute=self.compute, device=self.device)
+        return t
 
     def workspace_bytes(self, n):
         out = ctypes.c_size_t()
@@ -121,6 +176,9 @@ class Trial:
         return out
 
     def close(self):
+        for t in getattr(self, '_folded', {}).values():
+            t.close()
+        self._folded = {}
         if getattr(self, 'handle', None) is not None:
             self._lib.rfk_mlp_destroy(self.handle)
             self.handle = None
@@ -150,6 +208,21 @@ class Ensemble:
         self.fused = all(t.fused for t in self.trials)
         self.image_size = trials[0].image_size
         self.channels = trials[0].channels
+        self._folded = {}
+
+    def for_input(self, s_in):
+        """The ensemble of the same trials packed for ``s_in x s_in`` frames (see :meth:`Trial.for_input`)."""
+        s_in = int(s_in)
+        if s_in == self.image_size:
+            return self
+        e = self._folded.get(s_in)
+        if e is None:
+            e = self._folded[s_in] = Ensemble([t.for_input(s_in) for t in self.trials], total_trials=self.total_trials)
+        return e
+
+    @property
+    def can_fold_resize(self):
+        return all(t.compute not in ('f32', 'fp32') for t in self.trials)
 
     def workspace_bytes(self, n):
         out = ctypes.c_size_t()
@@ -282,7 +355,15 @@ class HostPipeline:
             if engine.image_size is None or ch != engine.channels:
                 raise ValueError('frames {} do not match the trials ({} channels)'.format(self.input_shape, engine.channels))
             if s_in != engine.image_size:
-                self._resize = (s_in, engine.image_size, ch)
+                can_fold = getattr(engine, 'can_fold_resize', None)
+                if can_fold is None:
+                    can_fold = getattr(engine, 'compute', 'f32') not in ('f32', 'fp32')
+                if can_fold:       # tensor-core trials: the resize folds into the first layer, frames go in as they are
+                    engine = engine.for_input(s_in)
+                    self.engine = engine
+                    d = engine.d
+                else:
+                    self._resize = (s_in, engine.image_size, ch)
                 d_host = s_in * s_in * ch
         self.d_host = d_host
         self._slots = []

@@ -48,6 +48,38 @@ def test_dropin_model_file_through_the_plugin_harness(S, tmp_path, monkeypatch, 
     model.destroy()
 
 
+def test_default_knob_resize_runs_on_the_gpu_path(tmp_path, monkeypatch):
+    """image_size 32 (the reference's FixedKnob, TfFeedForward.py:27) with 28 x 28 queries: tensor-core trials
+    fold the resize into their first layer (no resize pass at all), the fp32 trial resizes with the CUDA
+    kernel -- in neither case on the host."""
+    from rafiki_b200 import _native
+    monkeypatch.chdir(tmp_path)
+    p = synth.make_trial(6, 32, 1, 2, 64, data_kind='fashion')
+    frames = synth.make_queries(300, 28, 1, 'fashion', seed=9)                  # uint8 ndarray: binary ingress
+    want = np.asarray(ff.serve_batch([p], frames.tolist()))
+    r0, f0 = _native.launch_count('resize'), _native.launch_count('fused')
+    model, preds = serve_model_class(MODEL_FILE, 'TfFeedForward', TaskType.IMAGE_CLASSIFICATION, _wire(p), frames, _knobs(p))
+    assert np.abs(np.asarray(preds) - want).max() <= 2e-3
+    assert _native.launch_count('resize') == r0 and _native.launch_count('fused') > f0
+    assert np.abs(model.predict_array(frames) - want).max() <= 2e-3
+    model.destroy()
+    monkeypatch.setenv('RAFIKI_B200_COMPUTE', 'f32')
+    model, preds = serve_model_class(MODEL_FILE, 'TfFeedForward', TaskType.IMAGE_CLASSIFICATION, _wire(p), frames, _knobs(p))
+    assert np.abs(np.asarray(preds) - want).max() <= 1e-5
+    assert _native.launch_count('resize_u8_staged') > r0
+    model.destroy()
+    # the pinned pipeline in front of an ensemble of such trials: frames in as they arrive, bytes or ndarray
+    monkeypatch.delenv('RAFIKI_B200_COMPUTE')
+    params = [synth.make_trial(t, 32, 1, 2, 48 + 16 * t, data_kind='fashion') for t in range(2)]
+    ens = engine.Ensemble([engine.Trial(q) for q in params])
+    pipe = engine.HostPipeline(ens, max_batch=512, depth=2, input_shape=(28, 28))
+    got = pipe.serve(frames.tobytes())
+    assert np.abs(got - np.asarray(ff.serve_batch(params, frames.tolist()))).max() <= 2e-3
+    ens32 = engine.Ensemble([engine.Trial(q, compute='f32') for q in params])
+    got32 = engine.HostPipeline(ens32, max_batch=512, depth=1, input_shape=(28, 28)).serve(frames)
+    assert np.abs(got32 - np.asarray(ff.serve_batch(params, frames.tolist()))).max() <= 1e-5
+
+
 def test_dropin_loads_a_reference_made_h5_parameter_dict(tmp_path, monkeypatch):
     """What a reference train worker stored: {'h5_model_base64': model.save() bytes} (TfFeedForward.py:102-118)."""
     import base64

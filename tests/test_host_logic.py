@@ -178,6 +178,21 @@ def test_binary_frames_ingress_without_gpu():
         frames_as_uint8(np.zeros((1, 4, 4), np.float32))
 
 
+def test_resize_folds_into_the_first_layer():
+    """Pillow-NEAREST resize + BatchNormalization + first Dense layer == one Dense layer on the raw frames
+    (rafiki_b200.engine.fold_resize_into_params): checked against the oracle's resize-then-forward."""
+    from oracle import feedforward as ff
+    from rafiki_b200 import synth
+    from rafiki_b200.engine import fold_resize_into_params
+    for S, s_in, ch in ((32, 28, 1), (48, 28, 1), (32, 28, 3)):
+        p = synth.make_trial(3, S, ch, 2, 36, data_kind='fashion')
+        q = synth.make_queries(40, s_in, ch, 'fashion', seed=2)
+        want = ff.forward(p, ff.resize_as_images(q.tolist(), [S, S]), np.float64)
+        pf = fold_resize_into_params(p, s_in, ch)
+        assert pf['kernels'][0].shape[0] == s_in * s_in * ch and pf['image_size'] == s_in
+        assert np.abs(ff.forward(pf, q, np.float64) - want).max() <= 1e-6
+
+
 def test_plugin_contract_of_the_dropin_model_file():
     src = open(os.path.join(ROOT, 'examples', 'models', 'image_classification', 'TfFeedForward.py'), 'rb').read()
     cwd = os.getcwd()
