@@ -98,7 +98,9 @@ struct PairParams {
   int items_q, items_r;       // items per pair: pair p takes items_q (+ 1 if p < items_r), in order
   int off_w2, off_w3, off_raw, off_bias, off_out, off_bar;
   rfk::PeerHook hook;   // all zero: no hand-shake (see rfk_internal.cuh)
-  int debug;            // development (RFK_PAIR_DEBUG): 4 = skip the layer-1 MMAs
+  int debug;            // development (RFK_PAIR_DEBUG, timing experiments only): 4 skip the layer-1 MMAs, 8 no raw ring,
+                        // 16 no tensor-memory stores of A, 32 no softmax / output, 64 no conversion
+  unsigned int* prof;   // development (RFK_PAIR_PROF): per-warp segment cycle sums, [2 CTAs][20 warps][12]
   long long* trace;     // development (RFK_PAIR_TRACE): event timestamps of pair 0, [2 CTAs][5 roles][kTraceLen]
 };
 constexpr int kTraceLen = 1024;
@@ -108,6 +110,17 @@ constexpr int kTraceLen = 1024;
       P.trace[((int)blockIdx.x * 5 + (role)) * kTraceLen + trace_n] = (clock64() << 4) | (long long)(tag); \
       ++trace_n;                                                                                     \
     }                                                                                                \
+  } while (0)
+
+// Development profile (kDev, RFK_PAIR_PROF): cycles per segment of a role's loop, summed in registers
+// (no stores inside the loops), written once per warp at the end: prof[cta][warp][8].
+#define PROF(k)                                   \
+  do {                                            \
+    if (kDev) {                                   \
+      const uint32_t now_ = (uint32_t)clock();    \
+      prof_acc[k] += now_ - prof_t;               \
+      prof_t = now_;                              \
+    }                                             \
   } while (0)
 
 struct PBars {
@@ -172,7 +185,7 @@ __device__ __forceinline__ void mbar_expect_tx_elect(uint64_t* bar, uint32_t byt
 
 // kTrace: development build with event timestamps (a lane-0 region after every hand-off makes the
 // issuing loops divergent for the compiler, so the production instantiation must not contain it)
-template <bool kF16, bool kTrace>
+template <bool kF16, bool kTrace, bool kDev>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ CUtensorMap x_map) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -183,6 +196,9 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
   const int lane = threadIdx.x & 31;
   int trace_n = 0;
   (void)trace_n;
+  uint32_t prof_acc[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, prof_t = (uint32_t)clock();
+  (void)prof_acc;
+  (void)prof_t;
   const uint32_t rank = (uint32_t)blockIdx.x & 1u;      // == %cluster_ctarank for a cluster of 2 along x; 0 = leader
   const bool leader = rank == 0;
   if ((smem_u32(smem) & 1023u) != 0u || cluster_ctarank() != rank) {
@@ -222,6 +238,7 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
   constexpr uint32_t tmem_base = 0u;
   const uint32_t smem_base = smem_u32(smem);
   const int n_kb = P.n_kb;
+  const int dbg = kDev ? P.debug : 0;      // development switches (timing experiments; results are not valid)
 
   // ---- this pair's items: a contiguous range of (trial, pair tile) in trial-major order
   const int pair = (int)blockIdx.x >> 1;
@@ -248,8 +265,9 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
     int prev_t = 0, prev_pt = 0;
     auto finish_prev = [&]() {
       // logits (v3) + bias -> softmax -> this trial's probabilities, staged and stored with 16-byte stores
-      if (half == 0) {
+      if (half == 0 && !(dbg & 32)) {
         float z[CPAD];
+        PROF(4);
         const float inv = softmax16(v3, bias + 2 * HMAX, P.n_classes, z);
         const int C = P.n_classes;
         const float* stage = reinterpret_cast<const float*>(smem + P.off_out);
@@ -268,6 +286,7 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
 #pragma unroll
           for (int j = 0; j < CPAD; ++j) sts_f32_if(dst + 4u * j, __fdiv_rn(z[j] * inv, P.div_f), j < C);
         }
+        PROF(8);
         if (!may_store) {
           if (lane < P.hook.n_wait) {                 // one flag word per lane: the polls overlap
             const long long t0 = clock64();
@@ -284,6 +303,7 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
           may_store = true;
         }
         named_bar_sync(BAR_SOFTMAX, 128);
+        PROF(9);
         {
           const long long first = (long long)prev_pt * (2 * TILE_M) + (long long)rank * TILE_M;
           long long rows = P.n - first;
@@ -296,7 +316,9 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
           }
           store_tile_probs(obase + first * C, stage, (int)rows * C, row);
         }
+        PROF(10);
         named_bar_sync(BAR_SOFTMAX, 128);
+        PROF(11);
       }
     };
     auto fetch_prev_logits = [&](uint32_t parity) {
@@ -331,9 +353,12 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
         cur_t = it.t;
       }
       // ---- layer 1: acc1[buf] -> hidden
+      PROF(0);
       mbar_wait(&bars->acc1_full[buf], par2);
+      PROF(1);
       if (warp == 0) PTRACE(3, 1);
       if (have_prev) fetch_prev_logits((uint32_t)((item - 1) & 1));
+      PROF(2);
       if (warp == 0) PTRACE(3, 5);
       tc_fence_after_sync();
       {
@@ -344,11 +369,14 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
       tc_fence_before_sync();
       warp_arrive_leader(l_hid_ready);
       if (T.n_hidden != 2) warp_arrive_leader(l_acc1_empty0 + 8u * buf);
+      PROF(3);
       if (warp == 0) PTRACE(3, 2);
       if (have_prev) finish_prev();
+      PROF(4);
       if (warp == 0) PTRACE(3, 6);
       if (T.n_hidden == 2) {
         mbar_wait(&bars->acc2_full, acc2_phase);
+        PROF(5);
         if (warp == 0) PTRACE(3, 3);
         acc2_phase ^= 1u;
         tc_fence_after_sync();
@@ -358,6 +386,7 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
         tc_fence_before_sync();
         warp_arrive_leader(l_hid_ready);
         warp_arrive_leader(l_acc1_empty0 + 8u * buf);
+        PROF(6);
         if (warp == 0) PTRACE(3, 4);
       }
       have_prev = true;
@@ -392,13 +421,15 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
         const bool have = atom < P.n_atoms;                 // the ragged end of the row may leave this group nothing
         int live = (P.d - atom * ATOM_K + 15) >> 4;        // 16-byte chunks the MMAs will read
         live = live < 0 ? 0 : (live > 4 ? 4 : live);
-        mbar_wait(&bars->raw_full[rstage], rphase);
+        PROF(0);
+        if (!(dbg & 8)) mbar_wait(&bars->raw_full[rstage], rphase);
+        PROF(1);
         if (warp == kEpiWarps) PTRACE(0, 1);
         const uint32_t rsrc = (uint32_t)rstage * RAW_STAGE;
         uint32_t p[32];
 #pragma unroll
         for (int h2 = 0; h2 < 2; ++h2) {
-          if (live > 2 * h2) {
+          if (live > 2 * h2 && !(dbg & 64)) {
             const uint4 r0 = lds_u4(raw_chunk[2 * h2] + rsrc), r1 = lds_u4(raw_chunk[2 * h2 + 1] + rsrc);
             uint32_t* q = p + 16 * h2;
             q[0] = u8x2_to_op<kF16>(r0.x, 0);  q[1] = u8x2_to_op<kF16>(r0.x, 2);
@@ -411,20 +442,24 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
             q[14] = u8x2_to_op<kF16>(r1.w, 0); q[15] = u8x2_to_op<kF16>(r1.w, 2);
           }
         }
-        warp_arrive(&bars->raw_empty[rstage]);
+        if (!(dbg & 8)) warp_arrive(&bars->raw_empty[rstage]);
+        PROF(2);
         if (have) {
           const int ga = item * P.n_atoms + atom;          // global atom counter of this pair
           const int as = ga % A_STAGES;
           if (ga >= A_STAGES) mbar_wait(&bars->a_free[as], (uint32_t)(((ga / A_STAGES) - 1) & 1));
+          PROF(3);
           if (warp == kEpiWarps) PTRACE(0, 2);
           tc_fence_after_sync();
           const uint32_t dst = a_dst0 + (uint32_t)as * A_COLS;
 #pragma unroll
           for (int h2 = 0; h2 < 2; ++h2)
-            if (live > 2 * h2) tmem_st16(dst + 16u * h2, *reinterpret_cast<const uint32_t(*)[16]>(p + 16 * h2));
+            if (live > 2 * h2 && !(dbg & 16)) tmem_st16(dst + 16u * h2, *reinterpret_cast<const uint32_t(*)[16]>(p + 16 * h2));
           tmem_st_wait();
+          PROF(4);
           tc_fence_before_sync();
           warp_arrive_leader(l_a_full0 + 8u * as);
+          PROF(5);
           if (warp == kEpiWarps) PTRACE(0, 3);
         }
         if (++rstage == P.raw_stages) { rstage = 0; rphase ^= 1u; }
@@ -466,8 +501,10 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
         cur_t = it.t;
       }
       const int row0 = it.pt * (2 * TILE_M) + (int)rank * TILE_M;
-      for (int kb = 0; kb < n_kb; ++kb) {
+      for (int kb = 0; kb < n_kb && !(dbg & 8); ++kb) {
+        PROF(0);
         mbar_wait(&bars->raw_empty[rstage], rphase ^ 1u);
+        PROF(1);
         PTRACE(1, 1);
         tma_load_2d_expect_elect(smem + P.off_raw + rstage * RAW_STAGE, &x_map, kb * KB, row0, RAW_STAGE,
                                  &bars->raw_full[rstage]);
@@ -573,18 +610,23 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
       const int buf = item & 1;
       const uint32_t idesc1 = idesc_16bit_f32(kF16, 2 * TILE_M, T.h1_pad);
       const uint32_t d_tmem = tmem_base + COL_ACC1 + buf * HMAX;
+      PROF(0);
       mbar_wait(&bars->acc1_empty[buf], (uint32_t)(((item >> 1) & 1) ^ 1));
+      PROF(1);
       PTRACE(2, 4);
       for (int atom = 0; atom < P.n_atoms; ++atom, ++gs) {
         mbar_wait(&bars->a_full[as], aphase);
+        PROF(2);
         PTRACE(2, 1);
         tc_fence_after_sync();
         const int k16 = (P.d - atom * ATOM_K) >> 4;
         const uint32_t a = tmem_base + COL_A + (uint32_t)as * A_COLS;
         const uint32_t b = w1_lo0 + (uint32_t)atom * (W1_ATOM >> 4);
-        if (!(P.debug & 4)) mma4_f16_ts_pair_elect(d_tmem, a, desc_from_lo(b), idesc1, atom != 0, k16 < 4 ? k16 : 4);
+        if (!(dbg & 4)) mma4_f16_ts_pair_elect(d_tmem, a, desc_from_lo(b), idesc1, atom != 0, k16 < 4 ? k16 : 4);
+        PROF(3);
         PTRACE(2, 2);
         mma_commit_pair_elect(&bars->a_free[as]);
+        PROF(4);
         if (++as == A_STAGES) { as = 0; aphase ^= 1u; }
       }
       mma_commit_pair_elect(&bars->acc1_full[buf]);
@@ -612,24 +654,33 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
       }
       const int buf = item & 1;
       if (T.n_hidden == 2) {
+        PROF(0);
         mbar_wait(&bars->hid_ready, hid_phase);
+        PROF(1);
         PTRACE(4, 1);
         hid_phase ^= 1u;
         tc_fence_after_sync();
         issue_small_layer(tmem_base + COL_ACC1 + (uint32_t)buf * HMAX, w2_lo, (HHALF * 128u) >> 4,
                           idesc_16bit_f32(kF16, 2 * TILE_M, T.h2_pad), T.h1_pad >> 4);
         mma_commit_pair_elect(&bars->acc2_full);
+        PROF(2);
         PTRACE(4, 2);
       }
       mbar_wait(&bars->hid_ready, hid_phase);
+      PROF(3);
       PTRACE(4, 3);
       hid_phase ^= 1u;
       tc_fence_after_sync();
       const int hl_pad = T.n_hidden == 2 ? T.h2_pad : T.h1_pad;
       issue_small_layer(tmem_base + COL_ACC3, w3_lo, (uint32_t)W3_ATOM >> 4, idesc_16bit_f32(kF16, 2 * TILE_M, CPAD), hl_pad >> 4);
       mma_commit_pair_elect(&bars->acc3_full);
+      PROF(4);
       PTRACE(4, 4);
     }
+  }
+  if (kDev && P.prof != nullptr && blockIdx.x < 2 && lane == 0) {
+    PROF(7);
+    for (int k = 0; k < 12; ++k) P.prof[((int)blockIdx.x * 20 + warp) * 12 + k] = prof_acc[k];
   }
   __syncwarp();
   tc_fence_before_sync();
@@ -769,6 +820,13 @@ int pair_forward(rfk_mlp* const* trials, int w, int total_trials, const uint8_t*
     P.debug = dbg ? atoi(dbg) : 0;
   }
   const bool f16 = trials[0]->dtype == RFK_F16;
+  const char* prof_path = getenv("RFK_PAIR_PROF");
+  unsigned int* dprof = nullptr;
+  if (prof_path != nullptr && f16) {       // development aid: allocates and synchronises
+    RFK_CUDA_TRY(cudaMalloc(&dprof, 2 * 20 * 12 * sizeof(unsigned int)));
+    RFK_CUDA_TRY(cudaMemsetAsync(dprof, 0, 2 * 20 * 12 * sizeof(unsigned int), st));
+    P.prof = dprof;
+  }
   const char* trace_path = getenv("RFK_PAIR_TRACE");
   long long* dtrace = nullptr;
   const size_t trace_elems = 2 * 5 * kTraceLen;
@@ -782,11 +840,12 @@ int pair_forward(rfk_mlp* const* trials, int w, int total_trials, const uint8_t*
   RFK_REQUIRE(dev >= 0 && dev < 64, "pair kernel: device ordinal %d not supported", dev);
   static std::atomic<bool> attr_set[64];
   if (!attr_set[dev].load(std::memory_order_acquire)) {     // per device; setting it twice is harmless
-    RFK_CUDA_TRY(cudaFuncSetAttribute(fused_pair_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_MAX));
-    RFK_CUDA_TRY(cudaFuncSetAttribute(fused_pair_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_MAX));
-    RFK_CUDA_TRY(cudaFuncSetAttribute(fused_pair_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_MAX));
+    RFK_CUDA_TRY(cudaFuncSetAttribute(fused_pair_kernel<true, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_MAX));
+    RFK_CUDA_TRY(cudaFuncSetAttribute(fused_pair_kernel<true, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_MAX));
+    RFK_CUDA_TRY(cudaFuncSetAttribute(fused_pair_kernel<false, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_MAX));
     cudaFuncAttributes fa;
-    RFK_CUDA_TRY(cudaFuncGetAttributes(&fa, fused_pair_kernel<true, false>));
+    RFK_CUDA_TRY(cudaFuncSetAttribute(fused_pair_kernel<true, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_MAX));
+    RFK_CUDA_TRY(cudaFuncGetAttributes(&fa, fused_pair_kernel<true, false, false>));
     if (fa.numRegs * (kEpiWarps + kConvWarps + 4) < kEpiWarps * kRegsEpi + kConvWarps * kRegsConv + 4 * kRegsLight) {
       set_error("pair kernel was compiled with %d registers per thread; its setmaxnreg budget needs %d", fa.numRegs,
                 kRegsLaunch);
@@ -800,12 +859,30 @@ int pair_forward(rfk_mlp* const* trials, int w, int total_trials, const uint8_t*
   P.items_q = (int)(items / pairs);
   P.items_r = (int)(items % pairs);
   if (f16 && dtrace != nullptr)
-    fused_pair_kernel<true, true><<<2 * pairs, kThreads, L.total, st>>>(P, x_map);
+    fused_pair_kernel<true, true, false><<<2 * pairs, kThreads, L.total, st>>>(P, x_map);
+  else if (f16 && (P.debug != 0 || dprof != nullptr))
+    fused_pair_kernel<true, false, true><<<2 * pairs, kThreads, L.total, st>>>(P, x_map);
   else if (f16)
-    fused_pair_kernel<true, false><<<2 * pairs, kThreads, L.total, st>>>(P, x_map);
+    fused_pair_kernel<true, false, false><<<2 * pairs, kThreads, L.total, st>>>(P, x_map);
   else
-    fused_pair_kernel<false, false><<<2 * pairs, kThreads, L.total, st>>>(P, x_map);
+    fused_pair_kernel<false, false, false><<<2 * pairs, kThreads, L.total, st>>>(P, x_map);
   RFK_LAUNCH_CHECK("fused_pair_kernel");
+  if (dprof != nullptr) {
+    unsigned int hp[2 * 20 * 12];
+    RFK_CUDA_TRY(cudaMemcpyAsync(hp, dprof, sizeof(hp), cudaMemcpyDeviceToHost, st));
+    RFK_CUDA_TRY(cudaStreamSynchronize(st));
+    cudaFree(dprof);
+    FILE* f = fopen(prof_path, "w");
+    if (f) {
+      for (int c = 0; c < 2; ++c)
+        for (int wv = 0; wv < 20; ++wv) {
+          fprintf(f, "%d %d", c, wv);
+          for (int k = 0; k < 12; ++k) fprintf(f, " %u", hp[(c * 20 + wv) * 12 + k]);
+          fprintf(f, "\n");
+        }
+      fclose(f);
+    }
+  }
   if (dtrace != nullptr) {
     std::vector<long long> hall(trace_elems);
     RFK_CUDA_TRY(cudaMemcpyAsync(hall.data(), dtrace, trace_elems * sizeof(long long), cudaMemcpyDeviceToHost, st));
