@@ -126,25 +126,38 @@ __device__ __forceinline__ void warp_arrive2(uint64_t* bar_a, uint64_t* bar_b) {
   }
 }
 
-// Last layer: 16 accumulator columns + bias -> softmax over the first C of them.  z[j] = exp(logit_j - max)
-// for j < C, 0 otherwise; returns 1 / sum.  Branch-free on purpose: with `if (j < C)` around the
-// exponentials and the stores the compiler emitted one uniform branch per class, each re-deriving its
-// addresses from special registers (about 100 cycles apiece on the per-item critical path).
-__device__ __forceinline__ float softmax16(const uint32_t (&v3)[16], const float* b3, int C, float (&z)[16]) {
+// Last layer: 16 accumulator columns + bias -> softmax.  z[j] = exp(logit_j - max), returns 1 / sum.
+// The padded classes need no predicate: their bias entry in the packed image is -infinity (fused_prepare)
+// and their weight rows are zero, so their logit is -infinity and their exponential an exact zero.  The
+// whole function is a serial chain on one warp per SM sub-partition (about 5 cycles per instruction), so it
+// is kept short: one FFMA + ex2.approx per class, one approximate reciprocal; both are far inside the
+// tolerance of the 16-bit path (2e-3 on a probability) and identical in the two fused kernels.
+__device__ __forceinline__ float softmax16(const uint32_t (&v3)[16], const float* b3, int /*C*/, float (&z)[16]) {
+  const float4* b4 = reinterpret_cast<const float4*>(b3);
   float mx = -INFINITY;
 #pragma unroll
-  for (int j = 0; j < 16; ++j) {
-    z[j] = __uint_as_float(v3[j]) + b3[j];
-    mx = fmaxf(mx, j < C ? z[j] : -INFINITY);
+  for (int q = 0; q < 4; ++q) {
+    const float4 bb = b4[q];
+    z[4 * q + 0] = __uint_as_float(v3[4 * q + 0]) + bb.x;
+    z[4 * q + 1] = __uint_as_float(v3[4 * q + 1]) + bb.y;
+    z[4 * q + 2] = __uint_as_float(v3[4 * q + 2]) + bb.z;
+    z[4 * q + 3] = __uint_as_float(v3[4 * q + 3]) + bb.w;
   }
-  float sum = 0.f;
 #pragma unroll
-  for (int j = 0; j < 16; ++j) {
-    const float e = __expf(z[j] - mx);
-    z[j] = j < C ? e : 0.f;
-    sum += z[j];
+  for (int j = 0; j < 16; j += 2) mx = fmaxf(mx, fmaxf(z[j], z[j + 1]));
+  const float kLog2e = 1.4426950408889634f;
+  const float off = -mx * kLog2e;
+  float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+  for (int j = 0; j < 16; j += 2) {
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(z[j]) : "f"(fmaf(z[j], kLog2e, off)));
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(z[j + 1]) : "f"(fmaf(z[j + 1], kLog2e, off)));
+    s0 += z[j];
+    s1 += z[j + 1];
   }
-  return 1.0f / sum;
+  float inv;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(s0 + s1));
+  return inv;
 }
 // predicated 4-byte shared-memory store (no branch)
 __device__ __forceinline__ void sts_f32_if(uint32_t addr, float v, bool pred) {

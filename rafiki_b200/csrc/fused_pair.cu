@@ -16,7 +16,7 @@
 // the single-CTA kernel keeps in registers.
 //
 // Roles per CTA (640 threads, as in fused_trial.cu): epilogue x 8 warps, converters x 8 (uint8 ->
-// fp16 into tensor memory), loader (TMA of raw tiles; bulk copies of the weights at a trial
+// fp16 into tensor memory; a warp converts its rows of a whole raw stage, two groups alternate stages), loader (TMA of raw tiles; bulk copies of the weights at a trial
 // change), layer-1 MMA issuer and layers-2/3 MMA issuer (LEADER CTA only: one thread issues for
 // both CTAs), and a warp that forwards "weights landed" to the leader.  Hand-offs that cross the
 // pair (operands ready, accumulator drained) are arrivals on the leader's mbarriers through the
@@ -68,7 +68,7 @@ constexpr int kRegsEpi = 136, kRegsConv = 72, kRegsLight = 64;
 // setmaxnreg.inc only hands out what the CTA's own warps have given back (the launch allocation)
 static_assert(kEpiWarps * kRegsEpi + kConvWarps * kRegsConv + 4 * kRegsLight <= (kEpiWarps + kConvWarps + 4) * kRegsLaunch,
               "setmaxnreg budget exceeds the launch allocation");
-constexpr int BAR_SOFTMAX = 1;
+constexpr int BAR_STAGE_FULL = 1, BAR_STAGE_FREE = 2;
 
 constexpr int TMEM_COLS = 512;
 constexpr int COL_ACC1 = 0;     // 2 x 128: layer-1 accumulators (layer 2 accumulates into the drained buffer)
@@ -93,7 +93,7 @@ struct PairParams {
   long long n;
   double divisor;             // the stored value is float(p / divisor)
   float div_f, div_recip;     // divisor as float, and 1 / divisor when it is a power of two
-  int div_pow2;
+  int div_mode;               // 0: divisor 1, 1: a power of two (multiply by div_recip), 2: one correctly rounded division
   int d, n_kb, n_atoms, w, n_classes, n_pt, raw_stages;
   int items_q, items_r;       // items per pair: pair p takes items_q (+ 1 if p < items_r), in order
   int off_w2, off_w3, off_raw, off_bias, off_out, off_bar;
@@ -208,7 +208,7 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
   if (threadIdx.x == 0) {
     for (int s = 0; s < MAX_RAW_STAGES; ++s) {
       mbar_init(&bars->raw_full[s], 1);
-      mbar_init(&bars->raw_empty[s], kConvWarps);
+      mbar_init(&bars->raw_empty[s], kConvWarps / 2);    // the four warps of the group that owns the stage
     }
     for (int s = 0; s < A_STAGES; ++s) {
       mbar_init(&bars->a_full[s], kConvWarps);       // 4 warps of the owning group x 2 CTAs
@@ -263,63 +263,80 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
     bool have_prev = false;
     bool may_store = P.hook.n_wait == 0;      // output in a peer's memory: wait until the slots have been consumed
     int prev_t = 0, prev_pt = 0;
-    auto finish_prev = [&]() {
-      // logits (v3) + bias -> softmax -> this trial's probabilities, staged and stored with 16-byte stores
-      if (half == 0 && !(dbg & 32)) {
-        float z[CPAD];
-        PROF(4);
-        const float inv = softmax16(v3, bias + 2 * HMAX, P.n_classes, z);
+    // The probabilities of a finished item leave in two steps on different warps.  The four half-0 warps turn
+    // the logits into probabilities and stage them densely in shared memory (finish_math, between the two hidden
+    // epilogues of the NEXT item, while the tensor pipe works on its layer 2); the four half-1 warps, which have
+    // nothing to do at the end of an item, copy the staged tile to global memory with 16-byte stores
+    // (finish_store) -- off the item-to-item chain of the softmax warps.  Two named barriers hand the staging
+    // buffer back and forth (arrive on one side, sync on the other, 128 + 128 threads).
+    bool stage_used = false;
+    auto finish_math = [&]() {
+      float z[CPAD];
+      const float inv = softmax16(v3, bias + 2 * HMAX, P.n_classes, z);
+      PROF(8);
+      const int C = P.n_classes;
+      const uint32_t dst = smem_base + (uint32_t)P.off_out + (uint32_t)(row * C) * 4u;
+      // A lone trial of a larger ensemble (one trial per GPU) stores float(p / total) with ONE rounding of the
+      // exact quotient, which is what the single-CTA kernel's float64 division gives for at most 32 trials.
+      // A power-of-two total is an exact scaling; otherwise one correctly rounded float division.  (The
+      // float64 division itself costs ~10 us per launch on this path and must stay off it.)
+      float scale = inv;
+      if (P.div_mode == 1) scale = inv * P.div_recip;      // exact: a power of two
+#pragma unroll
+      for (int j = 0; j < CPAD; ++j) z[j] = P.div_mode == 2 ? __fdiv_rn(z[j] * inv, P.div_f) : z[j] * scale;
+      if (stage_used) named_bar_sync(BAR_STAGE_FREE, 256);
+      PROF(9);
+      if (C == 10) {                                        // the reference's task: five 8-byte stores, no predicates
+#pragma unroll
+        for (int j = 0; j < 10; j += 2)
+          asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(dst + 4u * j), "f"(z[j]), "f"(z[j + 1]) : "memory");
+      } else {
+#pragma unroll
+        for (int j = 0; j < CPAD; ++j) sts_f32_if(dst + 4u * j, z[j], j < C);
+      }
+      __threadfence_block();
+      named_bar_arrive(BAR_STAGE_FULL, 256);
+      stage_used = true;
+      PROF(10);
+    };
+    auto finish_store = [&]() {
+      if (!may_store) {
+        if (lane < P.hook.n_wait) {                 // one flag word per lane: the polls overlap
+          const long long t0 = clock64();
+          unsigned int v;
+          do {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(P.hook.wait_flags + lane) : "memory");
+            if (clock64() - t0 > 4000000000LL) {
+              printf("rafiki_b200: pair kernel timed out waiting for its output slot (block %d)\n", blockIdx.x);
+              __trap();
+            }
+          } while ((int)(v - P.hook.wait_value) < 0);
+        }
+        __syncwarp();
+        may_store = true;
+      }
+      named_bar_sync(BAR_STAGE_FULL, 256);
+      PROF(8);
+      {
         const int C = P.n_classes;
         const float* stage = reinterpret_cast<const float*>(smem + P.off_out);
-        const uint32_t dst = smem_base + (uint32_t)P.off_out + (uint32_t)(row * C) * 4u;
-        // A lone trial of a larger ensemble (one trial per GPU) stores float(p / total) with ONE rounding of the
-        // exact quotient, which is what the single-CTA kernel's float64 division gives for at most 32 trials.
-        // A power-of-two total is an exact scaling; otherwise one correctly rounded float division.  (The
-        // float64 division itself costs ~10 us per launch on this path and must stay off it.)
-        if (P.divisor == 1.0) {
-#pragma unroll
-          for (int j = 0; j < CPAD; ++j) sts_f32_if(dst + 4u * j, z[j] * inv, j < C);
-        } else if (P.div_pow2) {
-#pragma unroll
-          for (int j = 0; j < CPAD; ++j) sts_f32_if(dst + 4u * j, (z[j] * inv) * P.div_recip, j < C);
-        } else {
-#pragma unroll
-          for (int j = 0; j < CPAD; ++j) sts_f32_if(dst + 4u * j, __fdiv_rn(z[j] * inv, P.div_f), j < C);
+        const long long first = (long long)prev_pt * (2 * TILE_M) + (long long)rank * TILE_M;
+        long long rows = P.n - first;
+        rows = rows < 0 ? 0 : (rows < TILE_M ? rows : TILE_M);
+        float* obase = P.out + (long long)prev_t * P.trial_stride;
+        if (P.hook.n_owner > 0) {                  // scatter form: this tile's rows belong to one owner GPU
+          int j = 0;
+          while (j + 1 < P.hook.n_owner && prev_pt >= P.hook.owner_bound[j + 1]) ++j;
+          obase = P.hook.out_owner[j];
         }
-        PROF(8);
-        if (!may_store) {
-          if (lane < P.hook.n_wait) {                 // one flag word per lane: the polls overlap
-            const long long t0 = clock64();
-            unsigned int v;
-            do {
-              asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(P.hook.wait_flags + lane) : "memory");
-              if (clock64() - t0 > 4000000000LL) {
-                printf("rafiki_b200: pair kernel timed out waiting for its output slot (block %d)\n", blockIdx.x);
-                __trap();
-              }
-            } while ((int)(v - P.hook.wait_value) < 0);
-          }
-          __syncwarp();
-          may_store = true;
-        }
-        named_bar_sync(BAR_SOFTMAX, 128);
-        PROF(9);
-        {
-          const long long first = (long long)prev_pt * (2 * TILE_M) + (long long)rank * TILE_M;
-          long long rows = P.n - first;
-          rows = rows < 0 ? 0 : (rows < TILE_M ? rows : TILE_M);
-          float* obase = P.out + (long long)prev_t * P.trial_stride;
-          if (P.hook.n_owner > 0) {                  // scatter form: this tile's rows belong to one owner GPU
-            int j = 0;
-            while (j + 1 < P.hook.n_owner && prev_pt >= P.hook.owner_bound[j + 1]) ++j;
-            obase = P.hook.out_owner[j];
-          }
-          store_tile_probs(obase + first * C, stage, (int)rows * C, row);
-        }
-        PROF(10);
-        named_bar_sync(BAR_SOFTMAX, 128);
-        PROF(11);
+        store_tile_probs(obase + first * C, stage, (int)rows * C, row);
       }
+      named_bar_arrive(BAR_STAGE_FREE, 256);          // the loads of the staged tile are complete (their values were stored)
+      PROF(9);
+    };
+    auto finish_prev = [&]() {
+      if (dbg & 32) return;
+      if (half == 0) finish_math(); else finish_store();
     };
     auto fetch_prev_logits = [&](uint32_t parity) {
       // both halves wait: the hidden tile may not be overwritten before the layer-3 MMAs have read it
@@ -371,7 +388,7 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
       if (T.n_hidden != 2) warp_arrive_leader(l_acc1_empty0 + 8u * buf);
       PROF(3);
       if (warp == 0) PTRACE(3, 2);
-      if (have_prev) finish_prev();
+      if (have_prev && half == 0) finish_prev();       // probabilities of the previous item: math and staging
       PROF(4);
       if (warp == 0) PTRACE(3, 6);
       if (T.n_hidden == 2) {
@@ -389,6 +406,8 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
         PROF(6);
         if (warp == 0) PTRACE(3, 4);
       }
+      if (have_prev && half == 1) finish_prev();       // ... and their way out, on the warps that are idle now
+      PROF(7);
       have_prev = true;
       prev_t = it.t;
       prev_pt = it.pt;
@@ -401,69 +420,84 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
   } else if (warp < kEpiWarps + kConvWarps) {
     // =============================================================== converter warps (own 128 rows)
     asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsConv));
-    const int quarter = warp & 3;
-    const int khalf = (warp - kEpiWarps) >> 2;
+    // A converter's loop is a serial chain (barrier probe, shared-memory loads, byte permutes, tensor-memory
+    // stores and their wait, arrivals): its latency, not its instruction count, sets the pace.  So one warp
+    // converts its 32 rows of a WHOLE raw stage per turn (128 bytes per row = two 64-wide K atoms = two A
+    // stages, 8 independent 16-byte loads in flight), and the two groups of four warps take alternate raw
+    // stages: the chain is paid once per two atoms and two chains overlap.
+    const int cw = warp - kEpiWarps;
+    const int quarter = cw & 3;
+    const int par = cw >> 2;                                // this warp takes raw stages par, par + 2, ... of the pair's stream
     const int row = quarter * 32 + lane;
     const uint32_t raw_row = smem_base + (uint32_t)P.off_raw + (uint32_t)row * 128u;
     const uint32_t sw = (uint32_t)(row & 7);
-    uint32_t raw_chunk[4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) raw_chunk[j] = raw_row + ((((uint32_t)(4 * khalf + j)) ^ sw) << 4);
     const uint32_t a_dst0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + COL_A;
-    int rstage = 0;
+    uint32_t lane0 = lane == 0 ? 1u : 0u;
+    asm volatile("" : "+r"(lane0));                         // keep the flag in a register (no S2R in the loop)
+    int item = 0, kb = par;
+    while (kb >= n_kb) { kb -= n_kb; ++item; }
+    int rstage = par;                                       // raw_stages >= 3 > par
     uint32_t rphase = 0;
-    // A warp owns bytes [64 khalf, 64 khalf + 64) of its rows in every 128-byte raw stage, i.e. the K atom
-    // 2 kb + khalf of the item: one A stage (32 columns) of its own, handed to the issuer on its own barrier,
-    // so the ring turns over in 64-wide steps while a thread's work per raw stage stays the same.
-    for (int item = 0; item < n_items; ++item) {
-      for (int kb = 0; kb < n_kb; ++kb) {
-        const int atom = 2 * kb + khalf;
-        const bool have = atom < P.n_atoms;                 // the ragged end of the row may leave this group nothing
-        int live = (P.d - atom * ATOM_K + 15) >> 4;        // 16-byte chunks the MMAs will read
-        live = live < 0 ? 0 : (live > 4 ? 4 : live);
-        PROF(0);
-        if (!(dbg & 8)) mbar_wait(&bars->raw_full[rstage], rphase);
-        PROF(1);
-        if (warp == kEpiWarps) PTRACE(0, 1);
-        const uint32_t rsrc = (uint32_t)rstage * RAW_STAGE;
-        uint32_t p[32];
-#pragma unroll
-        for (int h2 = 0; h2 < 2; ++h2) {
-          if (live > 2 * h2 && !(dbg & 64)) {
-            const uint4 r0 = lds_u4(raw_chunk[2 * h2] + rsrc), r1 = lds_u4(raw_chunk[2 * h2 + 1] + rsrc);
-            uint32_t* q = p + 16 * h2;
-            q[0] = u8x2_to_op<kF16>(r0.x, 0);  q[1] = u8x2_to_op<kF16>(r0.x, 2);
-            q[2] = u8x2_to_op<kF16>(r0.y, 0);  q[3] = u8x2_to_op<kF16>(r0.y, 2);
-            q[4] = u8x2_to_op<kF16>(r0.z, 0);  q[5] = u8x2_to_op<kF16>(r0.z, 2);
-            q[6] = u8x2_to_op<kF16>(r0.w, 0);  q[7] = u8x2_to_op<kF16>(r0.w, 2);
-            q[8] = u8x2_to_op<kF16>(r1.x, 0);  q[9] = u8x2_to_op<kF16>(r1.x, 2);
-            q[10] = u8x2_to_op<kF16>(r1.y, 0); q[11] = u8x2_to_op<kF16>(r1.y, 2);
-            q[12] = u8x2_to_op<kF16>(r1.z, 0); q[13] = u8x2_to_op<kF16>(r1.z, 2);
-            q[14] = u8x2_to_op<kF16>(r1.w, 0); q[15] = u8x2_to_op<kF16>(r1.w, 2);
-          }
-        }
-        if (!(dbg & 8)) warp_arrive(&bars->raw_empty[rstage]);
-        PROF(2);
-        if (have) {
-          const int ga = item * P.n_atoms + atom;          // global atom counter of this pair
-          const int as = ga % A_STAGES;
-          if (ga >= A_STAGES) mbar_wait(&bars->a_free[as], (uint32_t)(((ga / A_STAGES) - 1) & 1));
-          PROF(3);
-          if (warp == kEpiWarps) PTRACE(0, 2);
-          tc_fence_after_sync();
-          const uint32_t dst = a_dst0 + (uint32_t)as * A_COLS;
-#pragma unroll
-          for (int h2 = 0; h2 < 2; ++h2)
-            if (live > 2 * h2 && !(dbg & 16)) tmem_st16(dst + 16u * h2, *reinterpret_cast<const uint32_t(*)[16]>(p + 16 * h2));
-          tmem_st_wait();
-          PROF(4);
-          tc_fence_before_sync();
-          warp_arrive_leader(l_a_full0 + 8u * as);
-          PROF(5);
-          if (warp == kEpiWarps) PTRACE(0, 3);
-        }
-        if (++rstage == P.raw_stages) { rstage = 0; rphase ^= 1u; }
+    auto convert32 = [&](uint32_t src, uint32_t c0, uint32_t dst) {      // 32 bytes of the row -> 16 columns
+      const uint4 r0 = lds_u4(src + ((c0 ^ sw) << 4)), r1 = lds_u4(src + (((c0 + 1u) ^ sw) << 4));
+      uint32_t q[16];
+      q[0] = u8x2_to_op<kF16>(r0.x, 0);  q[1] = u8x2_to_op<kF16>(r0.x, 2);
+      q[2] = u8x2_to_op<kF16>(r0.y, 0);  q[3] = u8x2_to_op<kF16>(r0.y, 2);
+      q[4] = u8x2_to_op<kF16>(r0.z, 0);  q[5] = u8x2_to_op<kF16>(r0.z, 2);
+      q[6] = u8x2_to_op<kF16>(r0.w, 0);  q[7] = u8x2_to_op<kF16>(r0.w, 2);
+      q[8] = u8x2_to_op<kF16>(r1.x, 0);  q[9] = u8x2_to_op<kF16>(r1.x, 2);
+      q[10] = u8x2_to_op<kF16>(r1.y, 0); q[11] = u8x2_to_op<kF16>(r1.y, 2);
+      q[12] = u8x2_to_op<kF16>(r1.z, 0); q[13] = u8x2_to_op<kF16>(r1.z, 2);
+      q[14] = u8x2_to_op<kF16>(r1.w, 0); q[15] = u8x2_to_op<kF16>(r1.w, 2);
+      tmem_st16(dst, q);
+    };
+    while (item < n_items) {
+      const int atom0 = 2 * kb;                             // always < n_atoms
+      const bool two = atom0 + 1 < P.n_atoms;               // the ragged end of the row may leave one atom only
+      const int ga = item * P.n_atoms + atom0;              // global atom counter of this pair
+      const int as0 = ga % A_STAGES, round0 = ga / A_STAGES;
+      const int as1 = as0 + 1 == A_STAGES ? 0 : as0 + 1, round1 = as0 + 1 == A_STAGES ? round0 + 1 : round0;
+      PROF(0);
+      if (!(dbg & 8)) mbar_wait(&bars->raw_full[rstage], rphase);
+      PROF(1);
+      if (warp == kEpiWarps) PTRACE(0, 1);
+      if (round0 > 0) mbar_wait(&bars->a_free[as0], (uint32_t)((round0 - 1) & 1));
+      if (two && round1 > 0) mbar_wait(&bars->a_free[as1], (uint32_t)((round1 - 1) & 1));
+      PROF(3);
+      if (warp == kEpiWarps) PTRACE(0, 2);
+      tc_fence_after_sync();
+      const uint32_t rsrc = raw_row + (uint32_t)rstage * RAW_STAGE;
+      const uint32_t dst0 = a_dst0 + (uint32_t)as0 * A_COLS, dst1 = a_dst0 + (uint32_t)as1 * A_COLS;
+      const int left = P.d - atom0 * ATOM_K;                // K elements of this row from here on (> 0)
+      if (left >= 2 * ATOM_K) {                             // the common case: both atoms whole
+        convert32(rsrc, 0u, dst0);
+        convert32(rsrc, 2u, dst0 + 16u);
+        convert32(rsrc, 4u, dst1);
+        convert32(rsrc, 6u, dst1 + 16u);
+      } else {                                              // the last raw stage of a row: only the 16-byte chunks the MMAs read
+        const int live = (left + 15) >> 4;                  // 1 .. 7 chunks
+        convert32(rsrc, 0u, dst0);
+        if (live > 2) convert32(rsrc, 2u, dst0 + 16u);
+        if (live > 4) convert32(rsrc, 4u, dst1);
+        if (live > 6) convert32(rsrc, 6u, dst1 + 16u);
       }
+      PROF(2);
+      __syncwarp();
+      if (lane0 && !(dbg & 8)) mbar_arrive(&bars->raw_empty[rstage]);      // the bytes are in registers
+      tmem_st_wait();
+      PROF(4);
+      tc_fence_before_sync();
+      __syncwarp();
+      if (lane0) {
+        mbar_arrive_cluster(l_a_full0 + 8u * as0);
+        if (two) mbar_arrive_cluster(l_a_full0 + 8u * as1);
+      }
+      PROF(5);
+      if (warp == kEpiWarps) PTRACE(0, 3);
+      kb += 2;
+      if (kb >= n_kb) { kb -= n_kb; ++item; if (kb >= n_kb) { kb -= n_kb; ++item; } }
+      rstage += 2;
+      if (rstage >= P.raw_stages) { rstage -= P.raw_stages; rphase ^= 1u; }
     }
   } else {
     asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsLight));
@@ -804,7 +838,7 @@ int pair_forward(rfk_mlp* const* trials, int w, int total_trials, const uint8_t*
     P.trial_stride = 0;
     P.divisor = (double)total_trials;
     P.div_f = (float)total_trials;
-    P.div_pow2 = (total_trials & (total_trials - 1)) == 0 ? 1 : 0;
+    P.div_mode = total_trials == 1 ? 0 : ((total_trials & (total_trials - 1)) == 0 ? 1 : 2);
     P.div_recip = 1.0f / (float)total_trials;
     if (g_hook_set) {          // the kernel itself waits for / publishes the peer hand-shake
       P.hook = g_hook;
@@ -814,6 +848,7 @@ int pair_forward(rfk_mlp* const* trials, int w, int total_trials, const uint8_t*
     P.out = static_cast<float*>(ws);
     P.trial_stride = (long long)n * C;
     P.divisor = 1.0;
+    P.div_mode = 0;
   }
   {
     const char* dbg = getenv("RFK_PAIR_DEBUG");

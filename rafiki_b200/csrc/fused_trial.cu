@@ -706,6 +706,7 @@ int fused_prepare(rfk_mlp* h) {
   rc = upload_vec(&s->w3, img);
   if (rc != RFK_OK) return rc;
   for (int j = 0; j < l3.out_pad && j < CPAD; ++j) bias[2 * HMAX + j] = l3.b_fold_host[j];
+  for (int j = h->n_classes; j < CPAD; ++j) bias[2 * HMAX + j] = -INFINITY;     // padded classes: see softmax16
   rc = upload_vec(&s->bias, bias);
   if (rc != RFK_OK) return rc;
   s->dev.w1 = s->w1;

@@ -74,7 +74,10 @@ __device__ __forceinline__ bool mbar_try_wait_hint(uint64_t* bar, uint32_t parit
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
   uint32_t spins = 0;
-  while (!mbar_try_wait_hint(bar, parity, 1000u)) {
+#ifndef RFK_MBAR_HINT_NS
+#define RFK_MBAR_HINT_NS 1000u
+#endif
+  while (!(RFK_MBAR_HINT_NS == 0u ? mbar_try_wait(bar, parity) : mbar_try_wait_hint(bar, parity, RFK_MBAR_HINT_NS))) {
     if (++spins > (1u << 22)) {
       printf("rafiki_b200: mbarrier wait timed out (block %d thread %d bar %u parity %u)\n", blockIdx.x,
              threadIdx.x, smem_u32(bar), parity);

@@ -1,7 +1,7 @@
 """Summarise RFK_PAIR_PROF files (development): cycles per loop segment of each role, pair 0."""
 import sys
 
-NAMES = {'epi': ['ovh', 'acc1 wait', 'acc3 fetch', 'epi1', 'fin:rest', 'acc2 wait', 'epi2', 'end', 'fin:math+sts', 'fin:bar1', 'fin:store', 'fin:bar2'],
+NAMES = {'epi': ['ovh', 'acc1 wait', 'acc3 fetch', 'epi1', 'fin:rest', 'acc2 wait', 'epi2', 'store-side', 'fin:math|wait full', 'fin:free wait|store', 'fin:sts', 'x'],
          'conv': ['ovh', 'raw wait', 'lds+cvt', 'a_free wait', 'sttm+wait', 'arrive', '-', 'end'],
          'load': ['issue', 'raw_empty wait', '', '', '', '', '', 'end'],
          'mma': ['ovh', 'acc1_empty wait', 'a_full wait', 'issue', 'commit', '', '', 'end'],
