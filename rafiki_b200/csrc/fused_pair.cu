@@ -41,7 +41,13 @@ using namespace fusedk;
 constexpr int TILE_M = 128;          // rows per CTA; a pair covers 256
 constexpr int ATOM_K = 64;
 constexpr int KB = 128;              // K elements per raw stage (one TMA box)
-constexpr int A_STAGES = 5;          // A operand ring in tensor memory: stages of ONE 64-wide K atom
+#ifndef RFK_DEV_A_STAGES
+#define RFK_DEV_A_STAGES 5
+#endif
+#ifndef RFK_DEV_ACC_STRIDE          // development: 64 frees tensor memory for a longer A ring (valid for <= 64 hidden units only)
+#define RFK_DEV_ACC_STRIDE 128
+#endif
+constexpr int A_STAGES = RFK_DEV_A_STAGES;   // A operand ring in tensor memory: stages of ONE 64-wide K atom
 constexpr int A_COLS = ATOM_K / 2;   // 32 columns per stage
 constexpr int MAX_RAW_STAGES = 6;
 constexpr int MIN_RAW_STAGES = 3;
@@ -72,7 +78,8 @@ constexpr int BAR_STAGE_FULL = 1, BAR_STAGE_FREE = 2;
 
 constexpr int TMEM_COLS = 512;
 constexpr int COL_ACC1 = 0;     // 2 x 128: layer-1 accumulators (layer 2 accumulates into the drained buffer)
-constexpr int COL_A = 256;      // A ring: A_STAGES x 32 columns
+constexpr int ACC_STRIDE = RFK_DEV_ACC_STRIDE;
+constexpr int COL_A = 2 * ACC_STRIDE;      // A ring: A_STAGES x 32 columns
 constexpr int COL_HID = 416;    // hidden activations (16-bit pairs): 64 columns
 constexpr int COL_ACC3 = 480;
 static_assert(COL_A + A_STAGES * A_COLS <= COL_HID && COL_HID + HMAX / 2 <= COL_ACC3 && COL_ACC3 + CPAD <= TMEM_COLS,
@@ -380,7 +387,7 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
       tc_fence_after_sync();
       {
         const int split = T.h1_pad < 64 ? T.h1_pad : 64;
-        epilogue_hidden<kF16>(lane_addr + COL_ACC1 + buf * HMAX, half ? split : 0, half ? T.h1_pad : split, bias,
+        epilogue_hidden<kF16>(lane_addr + COL_ACC1 + buf * ACC_STRIDE, half ? split : 0, half ? T.h1_pad : split, bias,
                               kF16 ? kSubnormalScale : 1.0f, hid_row_addr);
       }
       tc_fence_before_sync();
@@ -398,7 +405,7 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
         acc2_phase ^= 1u;
         tc_fence_after_sync();
         const int split = T.h2_pad < 64 ? T.h2_pad : 64;
-        epilogue_hidden<kF16>(lane_addr + COL_ACC1 + buf * HMAX, half ? split : 0, half ? T.h2_pad : split, bias + HMAX,
+        epilogue_hidden<kF16>(lane_addr + COL_ACC1 + buf * ACC_STRIDE, half ? split : 0, half ? T.h2_pad : split, bias + HMAX,
                               1.0f, hid_row_addr);
         tc_fence_before_sync();
         warp_arrive_leader(l_hid_ready);
@@ -539,7 +546,6 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
         PROF(0);
         mbar_wait(&bars->raw_empty[rstage], rphase ^ 1u);
         PROF(1);
-        PTRACE(1, 1);
         tma_load_2d_expect_elect(smem + P.off_raw + rstage * RAW_STAGE, &x_map, kb * KB, row0, RAW_STAGE,
                                  &bars->raw_full[rstage]);
         if (++rstage == P.raw_stages) { rstage = 0; rphase ^= 1u; }
@@ -556,6 +562,16 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
         warp_arrive_leader(l_w_ready);
         ++epoch;
         cur_t = it.t;
+      }
+    }
+    if (kTrace && P.trace != nullptr && blockIdx.x == 0) {
+      // development: this idle warp watches the A stages come back (exact arrival times of a_free)
+      int as = 0;
+      uint32_t ph = 0;
+      for (int n = 0; n < n_items * P.n_atoms; ++n) {
+        mbar_wait(&bars->a_free[as], ph);
+        PTRACE(1, 2);
+        if (++as == A_STAGES) { as = 0; ph ^= 1u; }
       }
     }
     // =============================================================== carried cross-GPU reduction (see PeerHook)
@@ -629,41 +645,50 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
     // =============================================================== layer-1 MMA issuer (leader CTA, for the pair)
     // A: tensor memory of each CTA (its own 128 rows); B: each CTA's half of W1, resident; D: tensor
     // memory of each CTA.  One commit per atom hands the A stage back to the converters of both CTAs.
-    const uint32_t w1_lo0 = desc_lo_sw128(smem_base);
-    int gs = 0, as = 0, epoch = 0, cur_t = -1;
-    uint32_t aphase = 0;
-    ItemIter it;
-    it.init(i_lo, P.n_pt);
-    for (int item = 0; item < n_items; ++item, it.next(P.n_pt)) {
-      const PairTrial& T = P.trial[it.t];
-      if (it.t != cur_t) {
-        mbar_wait(&bars->w_ready, (uint32_t)(epoch & 1));
-        ++epoch;
-        cur_t = it.t;
+    // The loop is a serial chain on the critical path (per atom: barrier probe, four MMAs, a commit); it has
+    // to turn in fewer cycles than the four MMAs take, so the common case (a whole 64-wide atom) is kept short.
+    {
+      const uint32_t w1_lo0 = desc_lo_sw128(smem_base);
+      const int n_whole = P.d >> 6;                        // atoms with all four K steps
+      int as = 0, epoch = 0, cur_t = -1;
+      uint32_t aphase = 0;
+      ItemIter it;
+      it.init(i_lo, P.n_pt);
+      for (int item = 0; item < n_items; ++item, it.next(P.n_pt)) {
+        const PairTrial& T = P.trial[it.t];
+        if (it.t != cur_t) {
+          mbar_wait(&bars->w_ready, (uint32_t)(epoch & 1));
+          ++epoch;
+          cur_t = it.t;
+        }
+        const int buf = item & 1;
+        const uint32_t idesc1 = idesc_16bit_f32(kF16, 2 * TILE_M, T.h1_pad);
+        const uint32_t d_tmem = tmem_base + COL_ACC1 + buf * ACC_STRIDE;
+        PROF(0);
+        mbar_wait(&bars->acc1_empty[buf], (uint32_t)(((item >> 1) & 1) ^ 1));
+        PROF(1);
+        PTRACE(2, 4);
+        uint32_t b = w1_lo0;
+        for (int atom = 0; atom < P.n_atoms; ++atom, b += (uint32_t)(W1_ATOM >> 4)) {
+          mbar_wait(&bars->a_full[as], aphase);
+          PROF(2);
+          PTRACE(2, 1);
+          tc_fence_after_sync();
+          const uint32_t a = tmem_base + COL_A + (uint32_t)as * A_COLS;
+          if (!(dbg & 4)) {
+            if (atom < n_whole)
+              mma4_f16_ts_pair_whole(d_tmem, a, b, idesc1, atom != 0);
+            else
+              mma4_f16_ts_pair_elect(d_tmem, a, desc_from_lo(b), idesc1, atom != 0, (P.d & (ATOM_K - 1)) >> 4);
+          }
+          PROF(3);
+          PTRACE(2, 2);
+          mma_commit_pair_elect(&bars->a_free[as]);
+          PROF(4);
+          if (++as == A_STAGES) { as = 0; aphase ^= 1u; }
+        }
+        mma_commit_pair_elect(&bars->acc1_full[buf]);
       }
-      const int buf = item & 1;
-      const uint32_t idesc1 = idesc_16bit_f32(kF16, 2 * TILE_M, T.h1_pad);
-      const uint32_t d_tmem = tmem_base + COL_ACC1 + buf * HMAX;
-      PROF(0);
-      mbar_wait(&bars->acc1_empty[buf], (uint32_t)(((item >> 1) & 1) ^ 1));
-      PROF(1);
-      PTRACE(2, 4);
-      for (int atom = 0; atom < P.n_atoms; ++atom, ++gs) {
-        mbar_wait(&bars->a_full[as], aphase);
-        PROF(2);
-        PTRACE(2, 1);
-        tc_fence_after_sync();
-        const int k16 = (P.d - atom * ATOM_K) >> 4;
-        const uint32_t a = tmem_base + COL_A + (uint32_t)as * A_COLS;
-        const uint32_t b = w1_lo0 + (uint32_t)atom * (W1_ATOM >> 4);
-        if (!(dbg & 4)) mma4_f16_ts_pair_elect(d_tmem, a, desc_from_lo(b), idesc1, atom != 0, k16 < 4 ? k16 : 4);
-        PROF(3);
-        PTRACE(2, 2);
-        mma_commit_pair_elect(&bars->a_free[as]);
-        PROF(4);
-        if (++as == A_STAGES) { as = 0; aphase ^= 1u; }
-      }
-      mma_commit_pair_elect(&bars->acc1_full[buf]);
     }
   } else if (warp == WARP_TAIL && leader) {
     // =============================================================== layers 2 and 3 (leader CTA, for the pair)
@@ -694,7 +719,7 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
         PTRACE(4, 1);
         hid_phase ^= 1u;
         tc_fence_after_sync();
-        issue_small_layer(tmem_base + COL_ACC1 + (uint32_t)buf * HMAX, w2_lo, (HHALF * 128u) >> 4,
+        issue_small_layer(tmem_base + COL_ACC1 + (uint32_t)buf * ACC_STRIDE, w2_lo, (HHALF * 128u) >> 4,
                           idesc_16bit_f32(kF16, 2 * TILE_M, T.h2_pad), T.h1_pad >> 4);
         mma_commit_pair_elect(&bars->acc2_full);
         PROF(2);

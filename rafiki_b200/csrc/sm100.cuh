@@ -379,6 +379,30 @@ __device__ __forceinline__ void mma_commit_pair_elect(uint64_t* bar) {
       : "memory");
 }
 
+// Four K steps of 16, always (the hot path of the layer-1 issuer: its loop is a serial chain on the critical
+// path).  Executed by the whole warp so that every operand stays in uniform registers; one elected lane
+// issues.  The descriptors of steps 2..4 differ in their low word only (start address + 32 bytes per step).
+__device__ __forceinline__ void mma4_f16_ts_pair_whole(uint32_t d_tmem, uint32_t a_tmem, uint32_t b_desc_lo, uint32_t idesc,
+                                                        uint32_t accumulate_first) {
+  constexpr uint32_t hi = (1024u >> 4) | (1u << 14) | (2u << 29);      // as desc_from_lo
+  asm volatile(
+      "{\n\t.reg .pred p, q, t;\n\t"
+      ".reg .b64 b1, b2, b3, b4;\n\t"
+      ".reg .b32 l2, l3, l4, a2, a3, a4;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "setp.eq.u32 t, 0, 0;\n\t"
+      "add.u32 l2, %2, 2;\n\tadd.u32 l3, %2, 4;\n\tadd.u32 l4, %2, 6;\n\t"
+      "add.u32 a2, %1, 8;\n\tadd.u32 a3, %1, 16;\n\tadd.u32 a4, %1, 24;\n\t"
+      "mov.b64 b1, {%2, %5};\n\tmov.b64 b2, {l2, %5};\n\tmov.b64 b3, {l3, %5};\n\tmov.b64 b4, {l4, %5};\n\t"
+      "@q tcgen05.mma.cta_group::2.kind::f16 [%0], [%1], b1, %3, p;\n\t"
+      "@q tcgen05.mma.cta_group::2.kind::f16 [%0], [a2], b2, %3, t;\n\t"
+      "@q tcgen05.mma.cta_group::2.kind::f16 [%0], [a3], b3, %3, t;\n\t"
+      "@q tcgen05.mma.cta_group::2.kind::f16 [%0], [a4], b4, %3, t;\n\t}" ::"r"(d_tmem),
+      "r"(a_tmem), "r"(b_desc_lo), "r"(idesc), "r"(accumulate_first), "r"(hi)
+      : "memory");
+}
+
 __device__ __forceinline__ bool elect_one() {
   uint32_t pred;
   asm volatile(

@@ -66,6 +66,30 @@ __global__ void __launch_bounds__(128, 1) ubench(int mode, int iters, int n_mma,
       }
       t = clock64() - t0;
     }
+  } else if (mode == 7) {
+    // probe of a phase that completed long ago, result feeds the next probe's address (serial chain)
+    if (warp == 0) {
+      if (lane == 0) mbar_arrive(&bar[0]);
+      __syncwarp();
+      uint32_t acc = 0;
+      const long long t0 = clock64();
+      for (int i = 0; i < iters; ++i) acc += mbar_try_wait(&bar[acc & 0u], 0u) ? 1u : 0u;
+      t = clock64() - t0 + (acc == 12345u ? 1 : 0);
+    }
+  } else if (mode == 8 || mode == 9 || mode == 10) {
+    // issue rate: n_mma MMAs + one commit per iteration, nobody waits until the end (bar[0] counts phases freely)
+    if (warp == 0) {
+      const uint32_t idesc = idesc_16bit_f32(true, 128, mode == 8 ? 128 : 16);    // 9, 10: tiny MMAs, the issue path shows
+      const uint32_t a_lo = desc_lo_sw128(smem_u32(smem)), b_lo = desc_lo_sw128(smem_u32(smem) + 16384);
+      const long long t0 = clock64();
+      for (int i = 0; i < iters; ++i) {
+        for (int k = 0; k < n_mma; k += 4) mma4_f16_ss_elect(0u, desc_from_lo(a_lo), desc_from_lo(b_lo), idesc, 1u, 4);
+        if (mode != 10) mma_commit_elect(&bar[0]);
+      }
+      mma_commit_elect(&bar[1]);
+      mbar_wait(&bar[1], 0);
+      t = clock64() - t0;
+    }
   } else {
     if (warp == 0) {
       const uint32_t idesc = idesc_16bit_f32(true, 128, 128);
@@ -112,6 +136,13 @@ int main() {
   run("ping-pong (2 hand-offs), try_wait + suspend hint", 0, 2000, 0);
   run("ping-pong (2 hand-offs), try_wait spin", 1, 2000, 0);
   run("ping-pong (2 hand-offs), test_wait spin", 2, 2000, 0);
+  run("try_wait on a completed phase, serial chain", 7, 2000, 0);
+  run("issue only: 4 MMAs (N128) + commit per iteration, no waits", 8, 2000, 4);
+  run("issue only: 8 MMAs (N128) + commit per iteration, no waits", 8, 2000, 8);
+  run("issue only: commit per iteration, no MMAs", 8, 2000, 0);
+  run("issue only: 4 MMAs (N16) + commit per iteration", 9, 2000, 4);
+  run("issue only: 4 MMAs (N16), no commit", 10, 2000, 4);
+  run("issue only: 16 MMAs (N16), no commit", 10, 2000, 16);
   run("commit only + wait (hint)", 5, 2000, 0);
   for (int n : {4, 8, 16}) {
     char buf[96];
