@@ -72,7 +72,7 @@ __global__ void __launch_bounds__(kThreads)
 decode_unit_kernel(const uint8_t* __restrict__ x, Out* __restrict__ y, int64_t n_units, int units_per_row,
                    const float* __restrict__ scale, const float* __restrict__ shift, int d, int use_smem) {
   constexpr int B = 16 / (int)sizeof(Out);        // input bytes per unit
-  constexpr int U = 4;                            // units per loop trip
+  constexpr int U = B == 8 ? 8 : 4;               // units per loop trip (loads in flight per thread)
   extern __shared__ __align__(16) float s_aff[];  // [2*d] when use_smem
   const float* sc = scale;
   const float* sh = shift;
@@ -198,40 +198,91 @@ resize_u8_kernel(const uint8_t* __restrict__ x, uint8_t* __restrict__ y, int64_t
 // output bytes through a per-block offset table and stores them as one 16-byte vector.  The one-byte-
 // per-thread kernel above ran at 4 % of HBM bandwidth.
 constexpr int kResizeSrcBytes = 32 * 1024;
+// When the image is enlarged, four consecutive output bytes come from at most eight consecutive source
+// bytes, so an output word is ONE byte permute of two aligned source words: the block keeps a second table
+// (source word index | PRMT selector << 16 per output word) and a thread builds its 16 output bytes with
+// one 16-byte table load, eight 4-byte loads and four permutes instead of sixteen byte gathers (the byte
+// gathers made the kernel shared-memory-issue bound at about half of the HBM rate).  A block whose table
+// has an output word that does not fit (a reduction, many channels) falls back to the byte gathers.
 __global__ void __launch_bounds__(kThreads)
 resize_u8_staged_kernel(const uint8_t* __restrict__ x, uint8_t* __restrict__ y, int64_t n, int s_in, int s_out, int ch,
                         int group) {
   extern __shared__ __align__(16) uint8_t rs_smem[];
   const int d_in = s_in * s_in * ch, d_out = s_out * s_out * ch;
   uint16_t* table = reinterpret_cast<uint16_t*>(rs_smem);                 // [d_out] source offset of each output byte
-  uint8_t* src = rs_smem + ((2 * d_out + 15) / 16) * 16;                    // [group][d_in]
+  uint32_t* wtab = reinterpret_cast<uint32_t*>(rs_smem + ((2 * d_out + 15) / 16) * 16);   // [d_out / 4]
+  uint8_t* src = reinterpret_cast<uint8_t*>(wtab) + d_out;                // 2 x ([group][d_in] + 16 bytes of slack)
   for (int j = threadIdx.x; j < d_out; j += kThreads) {
     const int c = j % ch, px = (j / ch) % s_out, py = j / (ch * s_out);
     const int sx = min(((2 * px + 1) * s_in) / (2 * s_out), s_in - 1);
     const int sy = min(((2 * py + 1) * s_in) / (2 * s_out), s_in - 1);
     table[j] = (uint16_t)((sy * s_in + sx) * ch + c);
   }
+  __syncthreads();
+  int bad = 0;
+  for (int w = threadIdx.x; w < d_out / 4; w += kThreads) {
+    const int o0 = table[4 * w], o1 = table[4 * w + 1], o2 = table[4 * w + 2], o3 = table[4 * w + 3];
+    const int base = min(min(o0, o1), min(o2, o3)) & ~3;
+    const int hi = max(max(o0, o1), max(o2, o3));
+    if (hi - base >= 8) bad = 1;
+    wtab[w] = (uint32_t)(base >> 2) |
+              ((uint32_t)((o0 - base) | ((o1 - base) << 4) | ((o2 - base) << 8) | ((o3 - base) << 12)) << 16);
+  }
+  const bool by_words = __syncthreads_or(bad) == 0;
   const int64_t n_groups = (n + group - 1) / group;
   const int vin = d_in / 16, vout = d_out / 16;
-  for (int64_t g = blockIdx.x; g < n_groups; g += gridDim.x) {
+  // Two source buffers: the 16-byte asynchronous copies of the NEXT group are in flight while this one is
+  // gathered, so a block never sits between "loaded" and "stored" with nothing outstanding.
+  const uint32_t buf_bytes = (uint32_t)group * (uint32_t)d_in + 16u;
+  auto prefetch = [&](int64_t g, int b) {
     const int64_t first = g * group;
     const int imgs = (int)(n - first < group ? n - first : group);
-    __syncthreads();                                                      // table ready / previous group consumed
-    const uint4* gsrc = reinterpret_cast<const uint4*>(x + first * d_in);
-    for (int v = threadIdx.x; v < imgs * vin; v += kThreads) reinterpret_cast<uint4*>(src)[v] = __ldg(gsrc + v);
-    __syncthreads();
-    uint4* gdst = reinterpret_cast<uint4*>(y + first * d_out);
-    for (int v = threadIdx.x; v < imgs * vout; v += kThreads) {
-      const int img = v / vout, o = (v - img * vout) * 16;
-      const uint8_t* s = src + img * d_in;
-      uint32_t w[4];
-#pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        const uint16_t* t = table + o + 4 * q;
-        w[q] = (uint32_t)s[t[0]] | ((uint32_t)s[t[1]] << 8) | ((uint32_t)s[t[2]] << 16) | ((uint32_t)s[t[3]] << 24);
-      }
-      gdst[v] = make_uint4(w[0], w[1], w[2], w[3]);
+    const uint8_t* gsrc = x + first * d_in;
+    const uint32_t dst = (uint32_t)__cvta_generic_to_shared(src + (size_t)b * buf_bytes);
+    for (int v = threadIdx.x; v < imgs * vin; v += kThreads)
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 16u * v), "l"(gsrc + 16 * (size_t)v) : "memory");
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  int cur = 0;
+  if ((int64_t)blockIdx.x < n_groups) prefetch(blockIdx.x, 0);
+  for (int64_t g = blockIdx.x; g < n_groups; g += gridDim.x, cur ^= 1) {
+    const int64_t first = g * group;
+    const int imgs = (int)(n - first < group ? n - first : group);
+    if (g + gridDim.x < n_groups) {
+      prefetch(g + gridDim.x, cur ^ 1);
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+    } else {
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
     }
+    __syncthreads();                                                      // this group's bytes (and the tables) are visible
+    const uint8_t* sbuf = src + (size_t)cur * buf_bytes;
+    uint4* gdst = reinterpret_cast<uint4*>(y + first * d_out);
+    if (by_words) {
+      for (int v = threadIdx.x; v < imgs * vout; v += kThreads) {
+        const int img = v / vout, ov = v - img * vout;
+        const uint32_t* s32 = reinterpret_cast<const uint32_t*>(sbuf + img * d_in);
+        const uint4 e = reinterpret_cast<const uint4*>(wtab)[ov];
+        uint4 o;
+        o.x = __byte_perm(s32[e.x & 0xffffu], s32[(e.x & 0xffffu) + 1], e.x >> 16);
+        o.y = __byte_perm(s32[e.y & 0xffffu], s32[(e.y & 0xffffu) + 1], e.y >> 16);
+        o.z = __byte_perm(s32[e.z & 0xffffu], s32[(e.z & 0xffffu) + 1], e.z >> 16);
+        o.w = __byte_perm(s32[e.w & 0xffffu], s32[(e.w & 0xffffu) + 1], e.w >> 16);
+        st_stream_16(reinterpret_cast<char*>(gdst + v), o);
+      }
+    } else {
+      for (int v = threadIdx.x; v < imgs * vout; v += kThreads) {
+        const int img = v / vout, o = (v - img * vout) * 16;
+        const uint8_t* s = sbuf + img * d_in;
+        uint32_t w[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const uint16_t* t = table + o + 4 * q;
+          w[q] = (uint32_t)s[t[0]] | ((uint32_t)s[t[1]] << 8) | ((uint32_t)s[t[2]] << 16) | ((uint32_t)s[t[3]] << 24);
+        }
+        gdst[v] = make_uint4(w[0], w[1], w[2], w[3]);
+      }
+    }
+    __syncthreads();                                                      // done with this buffer before it is refilled
   }
 }
 
@@ -245,7 +296,7 @@ int launch_decode(const uint8_t* x, Out* y, int64_t n, int d, int ld_out, const 
   if (s_in <= 0 && d % 16 == 0 && ld_out == d && aligned) {
     constexpr int B = 16 / (int)sizeof(Out);
     const int64_t n_units = n * (int64_t)(d / B);
-    const int64_t want = (n_units + 4 * kThreads - 1) / (4 * kThreads);
+    const int64_t want = (n_units + (B == 8 ? 8 : 4) * kThreads - 1) / ((B == 8 ? 8 : 4) * kThreads);
     const int grid = (int)(want < (int64_t)sms * 8 ? (want > 0 ? want : 1) : (int64_t)sms * 8);
     const int use_smem = (scale != nullptr && d <= kMaxSmemFeatures) ? 1 : 0;
     const size_t smem = use_smem ? (size_t)2 * d * sizeof(float) : 0;
@@ -305,19 +356,19 @@ extern "C" int rfk_resize_decode_u8(const uint8_t* x, void* y, int64_t n, int s_
     const int64_t want = (total + kThreads - 1) / kThreads;
     const int sms = rfk::num_sms();
     const int d_in = s_in * s_in * ch;
-    if (ld_out == d && d % 16 == 0 && d_in % 16 == 0 && d_in <= kResizeSrcBytes && d <= 32768 &&
+    if (ld_out == d && d % 16 == 0 && d_in % 16 == 0 && 2 * d_in <= kResizeSrcBytes && d <= 32768 &&
         ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y)) & 15) == 0) {
-      int group = kResizeSrcBytes / d_in;
-      group = group > 16 ? 16 : group;
-      const size_t smem = (size_t)((2 * d + 15) / 16) * 16 + (size_t)group * d_in;
+      int group = kResizeSrcBytes / (2 * d_in);                 // two buffers
+      group = group > 8 ? 8 : (group < 1 ? 1 : group);
+      const size_t smem = (size_t)((2 * d + 15) / 16) * 16 + (size_t)d + 2 * ((size_t)group * d_in + 16);
       const int64_t n_groups = (n + group - 1) / group;
-      const int g = (int)(n_groups < (int64_t)sms * 4 ? n_groups : (int64_t)sms * 4);
+      const int g = (int)(n_groups < (int64_t)sms * 8 ? n_groups : (int64_t)sms * 8);
       static std::atomic<bool> attr_set[64];
       int dev = 0;
       RFK_CUDA_TRY(cudaGetDevice(&dev));
       RFK_REQUIRE(dev >= 0 && dev < 64, "resize: device ordinal %d not supported", dev);
       if (!attr_set[dev].load(std::memory_order_acquire)) {     // setting it twice is harmless
-        RFK_CUDA_TRY(cudaFuncSetAttribute(resize_u8_staged_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+        RFK_CUDA_TRY(cudaFuncSetAttribute(resize_u8_staged_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 140 * 1024));
         attr_set[dev].store(true, std::memory_order_release);
       }
       resize_u8_staged_kernel<<<g, kThreads, smem, reinterpret_cast<cudaStream_t>(stream)>>>(
