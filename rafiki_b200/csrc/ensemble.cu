@@ -31,6 +31,9 @@ __device__ __forceinline__ float4 ld_stream_f4(const float* p) {
 template <int W>
 __global__ void __launch_bounds__(kThreads)
 ensemble_mean_vec4_kernel(const TrialPtrs ptrs, int w_runtime, int64_t n_vec, float* __restrict__ out, double divisor) {
+  // the next kernel of the stream may be a programmatic dependent (the pair kernel of the next batch): let its
+  // prologue start while this grid drains; it waits for this grid's completion before it touches global memory
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   const int w = W > 0 ? W : w_runtime;
   const int64_t stride = (int64_t)gridDim.x * kThreads;
   for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n_vec; i += stride) {

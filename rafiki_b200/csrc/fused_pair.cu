@@ -80,10 +80,16 @@ constexpr int TMEM_COLS = 512;
 constexpr int COL_ACC1 = 0;     // 2 x 128: layer-1 accumulators (layer 2 accumulates into the drained buffer)
 constexpr int ACC_STRIDE = RFK_DEV_ACC_STRIDE;
 constexpr int COL_A = 2 * ACC_STRIDE;      // A ring: A_STAGES x 32 columns
+#ifdef RFK_DEV_TIMING_ALIAS_ACC3     // development, TIMING ONLY (results are wrong): logits land in the layer-1 accumulator
+constexpr int COL_HID = 448;
+constexpr int COL_ACC3 = 0;
+static_assert(COL_A + A_STAGES * A_COLS <= COL_HID && COL_HID + HMAX / 2 <= TMEM_COLS, "tensor memory map");
+#else
 constexpr int COL_HID = 416;    // hidden activations (16-bit pairs): 64 columns
 constexpr int COL_ACC3 = 480;
 static_assert(COL_A + A_STAGES * A_COLS <= COL_HID && COL_HID + HMAX / 2 <= COL_ACC3 && COL_ACC3 + CPAD <= TMEM_COLS,
               "tensor memory map");
+#endif
 
 struct PairTrial {
   const uint8_t* w1;    // [n_atoms][h1_pad rows][128 B] swizzled (the single-CTA kernel's image)
@@ -245,6 +251,12 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
   constexpr uint32_t tmem_base = 0u;
   const uint32_t smem_base = smem_u32(smem);
   const int n_kb = P.n_kb;
+  // Launched as a programmatic dependent of the previous kernel of the stream: everything up to here touched
+  // shared and tensor memory only and may overlap that kernel's tail; the next kernel may start ITS prologue
+  // now.  Every warp waits for the previous grid before it touches global memory -- except the loader, which
+  // first starts the copies of this pair's first trial (parameters are immutable once a trial is loaded).
+  griddep_launch_dependents();
+  if (warp != WARP_LOAD) griddep_wait();
   const int dbg = kDev ? P.debug : 0;      // development switches (timing experiments; results are not valid)
 
   // ---- this pair's items: a contiguous range of (trial, pair tile) in trial-major order
@@ -538,6 +550,7 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
           bulk_g2s_elect(smem + P.off_w3 + a * W3_ATOM, T.w3 + (size_t)a * 2 * W3_ATOM + (size_t)rank * W3_ATOM, W3_ATOM,
                          &bars->w_full);
         bulk_g2s_elect(smem + P.off_bias, T.bias, BIAS_BYTES, &bars->w_full);
+        if (epoch == 0) griddep_wait();        // the queries (and everything after) may come from the previous kernel
         ++epoch;
         cur_t = it.t;
       }
@@ -918,14 +931,32 @@ int pair_forward(rfk_mlp* const* trials, int w, int total_trials, const uint8_t*
   if (items < pairs) pairs = (int)items;
   P.items_q = (int)(items / pairs);
   P.items_r = (int)(items % pairs);
-  if (f16 && dtrace != nullptr)
-    fused_pair_kernel<true, true, false><<<2 * pairs, kThreads, L.total, st>>>(P, x_map);
-  else if (f16 && (P.debug != 0 || dprof != nullptr))
-    fused_pair_kernel<true, false, true><<<2 * pairs, kThreads, L.total, st>>>(P, x_map);
-  else if (f16)
-    fused_pair_kernel<true, false, false><<<2 * pairs, kThreads, L.total, st>>>(P, x_map);
-  else
-    fused_pair_kernel<false, false, false><<<2 * pairs, kThreads, L.total, st>>>(P, x_map);
+  {
+    // a programmatic dependent of whatever precedes it in the stream: its prologue and first weight copies
+    // overlap the tail of that kernel (see griddep_wait in the kernel); RFK_NO_PDL=1 launches it ordinarily
+    static const bool pdl = getenv("RFK_NO_PDL") == nullptr;
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3((unsigned)(2 * pairs));
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = (size_t)L.total;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    cudaError_t le;
+    if (f16 && dtrace != nullptr)
+      le = cudaLaunchKernelEx(&cfg, fused_pair_kernel<true, true, false>, P, x_map);
+    else if (f16 && (P.debug != 0 || dprof != nullptr))
+      le = cudaLaunchKernelEx(&cfg, fused_pair_kernel<true, false, true>, P, x_map);
+    else if (f16)
+      le = cudaLaunchKernelEx(&cfg, fused_pair_kernel<true, false, false>, P, x_map);
+    else
+      le = cudaLaunchKernelEx(&cfg, fused_pair_kernel<false, false, false>, P, x_map);
+    RFK_CUDA_TRY(le);
+  }
   RFK_LAUNCH_CHECK("fused_pair_kernel");
   if (dprof != nullptr) {
     unsigned int hp[2 * 20 * 12];

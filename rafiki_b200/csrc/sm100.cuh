@@ -403,6 +403,13 @@ __device__ __forceinline__ void mma4_f16_ts_pair_whole(uint32_t d_tmem, uint32_t
       : "memory");
 }
 
+// Programmatic dependent launch (a kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization):
+// griddep_launch_dependents lets the NEXT kernel of the stream start its prologue as soon as every CTA of this
+// grid has executed it (or exited); griddep_wait blocks until the PREVIOUS grid has completed and its memory
+// is visible.  Both are no-ops for an ordinary launch.
+__device__ __forceinline__ void griddep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 __device__ __forceinline__ bool elect_one() {
   uint32_t pred;
   asm volatile(
