@@ -9,6 +9,8 @@
 // HBM-bound: (W + 1) * C * 4 algorithmic bytes per query.  16-byte loads from each of the
 // W trial buffers (which may be peer-GPU memory), W independent loads in flight per
 // thread, persistent grid.
+#include <stdlib.h>
+#include <string.h>
 #include "rfk_internal.cuh"
 
 namespace {
@@ -34,6 +36,7 @@ ensemble_mean_vec4_kernel(const TrialPtrs ptrs, int w_runtime, int64_t n_vec, fl
   // the next kernel of the stream may be a programmatic dependent (the pair kernel of the next batch): let its
   // prologue start while this grid drains; it waits for this grid's completion before it touches global memory
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");       // launched as a programmatic dependent itself (see the launch)
   const int w = W > 0 ? W : w_runtime;
   const int64_t stride = (int64_t)gridDim.x * kThreads;
   for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n_vec; i += stride) {
@@ -115,14 +118,28 @@ int ensemble_reduce(const float* const* probs, int w, int64_t n, int c, float* o
     const int64_t n_vec = elems / 4;
     const int64_t want = (n_vec + kThreads - 1) / kThreads;
     const int grid = (int)(want < (int64_t)sms * 8 ? want : (int64_t)sms * 8);
+    // a programmatic dependent of the kernel before it (normally the trial kernel that wrote `probs`): its
+    // blocks are placed as that kernel's CTAs leave and wait, at their top, for the whole grid to complete
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(kThreads);
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = getenv("RFK_NO_PDL") == nullptr ? 1 : 0;
+    cudaError_t le;
     switch (w) {
-      case 1: ensemble_mean_vec4_kernel<1><<<grid, kThreads, 0, st>>>(ptrs, w, n_vec, out, divisor); break;
-      case 2: ensemble_mean_vec4_kernel<2><<<grid, kThreads, 0, st>>>(ptrs, w, n_vec, out, divisor); break;
-      case 3: ensemble_mean_vec4_kernel<3><<<grid, kThreads, 0, st>>>(ptrs, w, n_vec, out, divisor); break;
-      case 4: ensemble_mean_vec4_kernel<4><<<grid, kThreads, 0, st>>>(ptrs, w, n_vec, out, divisor); break;
-      case 8: ensemble_mean_vec4_kernel<8><<<grid, kThreads, 0, st>>>(ptrs, w, n_vec, out, divisor); break;
-      default: ensemble_mean_vec4_kernel<0><<<grid, kThreads, 0, st>>>(ptrs, w, n_vec, out, divisor); break;
+      case 1: le = cudaLaunchKernelEx(&cfg, ensemble_mean_vec4_kernel<1>, ptrs, w, n_vec, out, divisor); break;
+      case 2: le = cudaLaunchKernelEx(&cfg, ensemble_mean_vec4_kernel<2>, ptrs, w, n_vec, out, divisor); break;
+      case 3: le = cudaLaunchKernelEx(&cfg, ensemble_mean_vec4_kernel<3>, ptrs, w, n_vec, out, divisor); break;
+      case 4: le = cudaLaunchKernelEx(&cfg, ensemble_mean_vec4_kernel<4>, ptrs, w, n_vec, out, divisor); break;
+      case 8: le = cudaLaunchKernelEx(&cfg, ensemble_mean_vec4_kernel<8>, ptrs, w, n_vec, out, divisor); break;
+      default: le = cudaLaunchKernelEx(&cfg, ensemble_mean_vec4_kernel<0>, ptrs, w, n_vec, out, divisor); break;
     }
+    RFK_CUDA_TRY(le);
     RFK_LAUNCH_CHECK("ensemble_mean_vec4_kernel");
   } else {
     const int64_t want = (elems + kThreads - 1) / kThreads;
