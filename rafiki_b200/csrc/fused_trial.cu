@@ -245,6 +245,10 @@ fused_ensemble_kernel(const __grid_constant__ FusedParams P, const __grid_consta
     __trap();
   }
   constexpr uint32_t tmem_base = 0u;
+  // launched as a programmatic dependent of the previous kernel of the stream (see fused_pair.cu): the set-up
+  // above overlapped that kernel's tail; nothing touches global memory before the previous grid is complete
+  griddep_launch_dependents();
+  griddep_wait();
 
   const int n_kb = P.n_kb;
   // Work assignment.  Normal: CTA b takes tiles b, b + grid, ... and runs all trials of a tile back
@@ -856,10 +860,23 @@ int fused_forward(rfk_mlp* const* trials, int w, int total_trials, const uint8_t
     for (int i = 0; i < PF_COUNT; ++i) fprintf(stderr, "[rfk prof]   %-18s %10.0f\n", names[i], hprof[i] / items);
     return RFK_OK;
   }
-  if (trials[0]->dtype == RFK_F16)
-    fused_ensemble_kernel<true, false><<<grid, kThreads, SMEM_BYTES, st>>>(P, x_map);
-  else
-    fused_ensemble_kernel<false, false><<<grid, kThreads, SMEM_BYTES, st>>>(P, x_map);
+  {
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = SMEM_BYTES;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = getenv("RFK_NO_PDL") == nullptr ? 1 : 0;
+    if (trials[0]->dtype == RFK_F16)
+      RFK_CUDA_TRY(cudaLaunchKernelEx(&cfg, fused_ensemble_kernel<true, false>, P, x_map));
+    else
+      RFK_CUDA_TRY(cudaLaunchKernelEx(&cfg, fused_ensemble_kernel<false, false>, P, x_map));
+  }
   RFK_LAUNCH_CHECK("fused_ensemble_kernel");
   if (split) {
     // kernel 3 over the W per-trial outputs: same float64 sum and rounding as the in-kernel mean
