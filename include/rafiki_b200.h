@@ -241,6 +241,15 @@ int rfk_peer_ensemble_step_pipelined(rfk_peer_t* p, rfk_mlp_t* const* trials, in
                                      const uint8_t* x, int64_t n, void* workspace,
                                      size_t workspace_bytes, float** prev_result, void* stream);
 int rfk_peer_flush(rfk_peer_t* p, float** result, void* stream);
+/*
+ * A promise by the caller about rfk_peer_ensemble_step_pipelined: the query batches handed to it are complete
+ * before the call BEFORE it was enqueued (resident batches, or batches gathered two steps ahead).  The trial
+ * kernel of a step then starts while the previous step's kernel is still finishing (it is launched as a
+ * programmatic dependent and, with this promise, never waits for the previous grid: every other dependency
+ * between steps already goes through the flag words).  Default off: the kernel waits for the previous kernel
+ * of its stream before it reads the queries.  No counterpart in the reference (its workers never overlap).
+ */
+int rfk_peer_set_inputs_resident(rfk_peer_t* p, int on);
 
 #ifdef __cplusplus
 }

@@ -68,6 +68,7 @@ PROTOTYPES = {
     'rfk_peer_ensemble_step': (_i, [_vp, _c.POINTER(_vp), _i, _i, _vp, _i64, _vp, _sz, _c.POINTER(_vp), _vp]),
     'rfk_peer_ensemble_step_pipelined': (_i, [_vp, _c.POINTER(_vp), _i, _i, _vp, _i64, _vp, _sz, _c.POINTER(_vp), _vp]),
     'rfk_peer_flush': (_i, [_vp, _c.POINTER(_vp), _vp]),
+    'rfk_peer_set_inputs_resident': (_i, [_vp, _i]),
 }
 
 

@@ -256,7 +256,7 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
   // now.  Every warp waits for the previous grid before it touches global memory -- except the loader, which
   // first starts the copies of this pair's first trial (parameters are immutable once a trial is loaded).
   griddep_launch_dependents();
-  if (warp != WARP_LOAD) griddep_wait();
+  if (warp != WARP_LOAD && !P.hook.no_grid_wait) griddep_wait();
   const int dbg = kDev ? P.debug : 0;      // development switches (timing experiments; results are not valid)
 
   // ---- this pair's items: a contiguous range of (trial, pair tile) in trial-major order
@@ -550,7 +550,7 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
           bulk_g2s_elect(smem + P.off_w3 + a * W3_ATOM, T.w3 + (size_t)a * 2 * W3_ATOM + (size_t)rank * W3_ATOM, W3_ATOM,
                          &bars->w_full);
         bulk_g2s_elect(smem + P.off_bias, T.bias, BIAS_BYTES, &bars->w_full);
-        if (epoch == 0) griddep_wait();        // the queries (and everything after) may come from the previous kernel
+        if (epoch == 0 && !P.hook.no_grid_wait) griddep_wait();        // the queries (and everything after) may come from the previous kernel
         ++epoch;
         cur_t = it.t;
       }

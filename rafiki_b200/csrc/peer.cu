@@ -125,6 +125,8 @@ __global__ void peer_signal_kernel(const FlagPtrs flags, int count, unsigned int
 }
 
 __global__ void peer_wait_kernel(const unsigned int* done_flags, int world, unsigned int step) {
+  // it reads nothing but the flags: a kernel queued behind it as a programmatic dependent may start at once
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   if (threadIdx.x < world) {
     if (!spin_until_ge(done_flags + threadIdx.x, step)) {
       printf("rafiki_b200: peer wait timed out on rank %d (step %u)\n", (int)threadIdx.x, step);
@@ -272,14 +274,14 @@ PeerLayout peer_layout(int world, int64_t max_n, int d, int n_classes) {
   L.off_flags = off;
   // flag words: [0,G) partials ready | [G,2G) slice in place | [2G] block counter | [2G+1,3G+1) query slice ready |
   //             [3G+1,4G+1) rank's partial means have arrived in its slot (on every owner) | [4G+1,5G+1) owner j has
-  //             consumed its slots (on every rank) | [5G+1] block counter of the trial kernel | [5G+2] block counter of
+  //             consumed its slots (on every rank) | [5G+1] spare | [6G+3,6G+6) block counters of the trial kernel (step % 3) | [5G+2] block counter of
   //             the gather-sum kernel | [5G+3,6G+3) rank's rows of the result are in place (on the root)
   L.f_arrived = 3 * world + 1;
   L.f_consumed = 4 * world + 1;       // G words: owner j has consumed the slots it holds
-  L.f_counter = 5 * world + 1;
+  L.f_counter = 6 * world + 3;         // three words: the trial kernels of consecutive steps may overlap (step % 3)
   L.f_sumcounter = 5 * world + 2;
   L.f_done = 5 * world + 3;           // G words (root): rank j's rows of the result are in place
-  off += ((size_t)(6 * world + 4) * sizeof(unsigned int) + 255) / 256 * 256;
+  off += ((size_t)(6 * world + 8) * sizeof(unsigned int) + 255) / 256 * 256;
   L.total = off;
   return L;
 }
@@ -395,6 +397,7 @@ struct rfk_peer {
   unsigned int pending_step = 0;
   int64_t pending_n = 0;
   float* held_result = nullptr;
+  bool inputs_resident = false;            // rfk_peer_set_inputs_resident
 };
 
 extern "C" int rfk_peer_block_bytes(int world, int64_t max_n, int d, int n_classes, size_t* out) {
@@ -489,7 +492,8 @@ inline void owner_bounds(int64_t n, int G, int* bound) {
 // Scatter form, trial kernel of step `step`: every tile's partial means go to the owner of its rows.  With
 // carry_step != 0 the kernel also carries the reduction of that earlier step (batch carry_n) in its idle warp.
 int scatter_launch(rfk_peer* p, rfk_mlp_t* const* trials, int total_trials, const uint8_t* x, int64_t n, void* workspace,
-                   size_t workspace_bytes, unsigned int step, unsigned int carry_step, int64_t carry_n, void* stream) {
+                   size_t workspace_bytes, unsigned int step, unsigned int carry_step, int64_t carry_n, bool overlap,
+                   void* stream) {
   const int G = p->world, k = (int)(step % 3);
   unsigned int* my_flags = reinterpret_cast<unsigned int*>(p->base[p->rank] + p->L.off_flags);
   unsigned int* root_flags = reinterpret_cast<unsigned int*>(p->base[p->root] + p->L.off_flags);
@@ -497,7 +501,7 @@ int scatter_launch(rfk_peer* p, rfk_mlp_t* const* trials, int total_trials, cons
   memset(&hook, 0, sizeof(hook));
   hook.wait_value = step >= 3 ? step - 3 : 0;
   hook.signal_value = step;
-  hook.counter = my_flags + p->L.f_counter;
+  hook.counter = my_flags + p->L.f_counter + k;
   hook.wait_flags = my_flags + p->L.f_consumed;          // one word per owner
   hook.n_wait = G;
   hook.n_signal = G;
@@ -533,6 +537,9 @@ int scatter_launch(rfk_peer* p, rfk_mlp_t* const* trials, int total_trials, cons
     if (dbg & 8) hook.n_wait = hook.n_signal = 0;
     if (dbg & 16) hook.carry_v_hi = hook.carry_v_lo;      // hand-shake of the carried reduction without its loads and stores
   }
+  // overlap with the previous step's kernel only when both fill the chip (then a kernel three steps back, whose
+  // block counter this one reuses, has certainly left: every CTA of a step replaces a CTA of the step before)
+  hook.no_grid_wait = overlap && (n + 255) / 256 >= rfk::num_sms() / 2 ? 1 : 0;
   rfk::set_peer_hook(&hook);
   const int rc = rfk_ensemble_forward(trials, 1, total_trials, x, n, hook.out_owner[p->rank], workspace, workspace_bytes, stream);
   if (rfk::peer_hook_pending()) {      // the call did not reach the pair kernel after all
@@ -615,7 +622,7 @@ extern "C" int rfk_peer_ensemble_step(rfk_peer_t* p, rfk_mlp_t* const* trials, i
     const bool scatter = scatter_capable(p, trials, w, total_trials, n);
     const unsigned int wait_value = step >= 2 ? step - 2 : 0;
     if (scatter) {
-      int rc = scatter_launch(p, trials, total_trials, x, n, workspace, workspace_bytes, step, 0, 0, stream);
+      int rc = scatter_launch(p, trials, total_trials, x, n, workspace, workspace_bytes, step, 0, 0, false, stream);
       if (rc != RFK_OK) return rc;
       rc = scatter_sum(p, step, n, stream);
       if (rc != RFK_OK) return rc;
@@ -723,20 +730,44 @@ extern "C" int rfk_peer_ensemble_step_pipelined(rfk_peer_t* p, rfk_mlp_t* const*
   p->held_result = nullptr;
   const unsigned int step = ++p->rstep;
   const unsigned int carry = p->pending_step;
-  const int rc = scatter_launch(p, trials, total_trials, x, n, workspace, workspace_bytes, step, carry, p->pending_n, stream);
+  const int rc = scatter_launch(p, trials, total_trials, x, n, workspace, workspace_bytes, step, carry, p->pending_n,
+                                p->inputs_resident, stream);
   if (rc != RFK_OK) return rc;
   if (carry != 0) {
     static const int dbg = []() { const char* e = getenv("RFK_PEER_DEBUG"); return e ? atoi(e) : 0; }();
     if (p->rank == p->root && !(dbg & 1)) {      // every rank's rows of the carried step are in place before the caller reads them
       unsigned int* root_flags = reinterpret_cast<unsigned int*>(p->base[p->root] + p->L.off_flags);
-      const int rc2 = rfk_peer_wait_flags(root_flags + p->L.f_done, p->world, carry, stream);
-      if (rc2 != RFK_OK) return rc2;
+      if (p->inputs_resident) {
+        // queued as a programmatic dependent: the stream still does not pass it before the rows are in place, but
+        // the next step's trial kernel need not wait for it to END before it starts
+        cudaLaunchConfig_t cfg;
+        memset(&cfg, 0, sizeof(cfg));
+        cfg.gridDim = dim3(1);
+        cfg.blockDim = dim3(32);
+        cfg.stream = reinterpret_cast<cudaStream_t>(stream);
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        RFK_CUDA_TRY(cudaLaunchKernelEx(&cfg, peer_wait_kernel, (const unsigned int*)(root_flags + p->L.f_done), p->world, carry));
+        RFK_LAUNCH_CHECK("peer_wait_kernel");
+      } else {
+        const int rc2 = rfk_peer_wait_flags(root_flags + p->L.f_done, p->world, carry, stream);
+        if (rc2 != RFK_OK) return rc2;
+      }
     }
     prev = reinterpret_cast<float*>(p->base[p->rank] + p->L.off_result[carry & 1]);
   }
   p->pending_step = step;
   p->pending_n = n;
   if (prev_result != nullptr) *prev_result = prev;
+  return RFK_OK;
+}
+
+extern "C" int rfk_peer_set_inputs_resident(rfk_peer_t* p, int on) {
+  RFK_REQUIRE(p != nullptr, "peer_set_inputs_resident: NULL argument");
+  p->inputs_resident = on != 0;
   return RFK_OK;
 }
 

@@ -72,6 +72,11 @@ struct PeerHook {
   long long carry_v_lo, carry_v_hi;
   unsigned int carry_step;
   int n_carry;
+  // The caller guarantees that nothing this launch reads (the queries) was produced by earlier work of its
+  // stream and every cross-launch dependency goes through the flags above: the kernel, launched as a
+  // programmatic dependent, then does not wait for the previous grid at all (its first CTAs run while the last
+  // CTAs of the previous step finish and publish their flags).
+  int no_grid_wait;
 };
 void set_peer_hook(const PeerHook* hook);     // thread-local; consumed (and cleared) by the next pair_forward with w == 1
 bool peer_hook_pending();

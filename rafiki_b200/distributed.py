@@ -161,6 +161,12 @@ class PeerEnsemble:
         prev_n, self._last_n = self._last_n, n
         return self._view(res.value, prev_n)
 
+    def set_inputs_resident(self, on=True):
+        """Promise that the batches given to ``step_pipelined`` are complete before the PREVIOUS call was
+        enqueued (resident batches): the trial kernel of a step may then start while the previous step's
+        kernel is finishing (``rfk_peer_set_inputs_resident``).  Off by default."""
+        self._check(self._lib.rfk_peer_set_inputs_resident(self._ctx, 1 if on else 0))
+
     def flush(self):
         res = ctypes.c_void_p()
         self._check(self._lib.rfk_peer_flush(self._ctx, ctypes.byref(res),

@@ -80,6 +80,28 @@ def main():
             print('pipelined batch %d n %6d: vs single GPU %.3e' % (i, X.shape[0], e), flush=True)
             ok = ok and e <= 1e-6 and got[i].shape == want.shape
     dist.barrier()
+    # the same with resident batches and the promise that lets consecutive trial kernels overlap
+    resident = [torch.from_numpy(X).to(dev) for X in batches]
+    torch.cuda.synchronize()
+    dist.barrier()
+    peer.set_inputs_resident(True)
+    got = []
+    for rep in range(3):
+        for x in resident:
+            prev = peer.step_pipelined(x)
+            if prev is not None:
+                got.append(prev.clone())
+    got.append(peer.flush().clone())
+    peer.set_inputs_resident(False)
+    torch.cuda.synchronize()
+    if rank == 0:
+        for i, g in enumerate(got):
+            want = full.forward(resident[i % len(resident)])
+            e = float((g.double() - want.double()).abs().max().item())
+            worst = max(worst, e)
+            ok = ok and e <= 1e-6 and g.shape == want.shape
+        print('pipelined, resident batches, overlapping kernels: %d results, worst vs single GPU %.3e' % (len(got), worst), flush=True)
+    dist.barrier()
     verdict = torch.tensor([1 if ok else 0], device=dev)
     dist.broadcast(verdict, 0)
     if rank == 0:

@@ -42,6 +42,8 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return t[0].item(), t[1].item()
 
+    if os.environ.get('RFK_RESIDENT'):
+        peer.set_inputs_resident(True)
     if os.environ.get('RFK_PEER_DEBUG'):
         c = timed(lambda i: peer.step_pipelined(xs[i % 4]))
         if rank == 0:
@@ -51,6 +53,12 @@ def main():
     b = timed(lambda i: peer.step(xs[i % 4]))
     c = timed(lambda i: peer.step_pipelined(xs[i % 4]))
     peer.flush()
+    torch.cuda.synchronize()
+    peer.set_inputs_resident(True)
+    c2 = timed(lambda i: peer.step_pipelined(xs[i % 4]))
+    peer.flush()
+    if rank == 0:
+        print('world %d: pipelined peer step with resident inputs (kernels overlap) %.1f us' % (world, c2[0]), flush=True)
     torch.cuda.synchronize()
     if rank == 0:
         print('world %d: pipelined peer step %.1f us (host %.1f us per call)' % (world, c[0], c[1]), flush=True)
