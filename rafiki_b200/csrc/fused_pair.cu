@@ -758,7 +758,7 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
   tc_fence_before_sync();
   cluster_sync_all();            // neither CTA leaves (or frees tensor memory) while the other may still signal it
   if (warp == WARP_MMA) tmem_dealloc_pair<TMEM_COLS>(tmem_base);
-  if (P.hook.n_signal > 0 && threadIdx.x == 0) {
+  if ((P.hook.n_signal > 0 || P.hook.n_carry > 0) && threadIdx.x == 0) {
     // Every store of this CTA (its tiles' outputs, its share of the carried sums) precedes the cluster barrier
     // above.  ONE system-scope fence per CTA, then the last CTA out publishes the flags with plain stores: a
     // release store per flag would pay a system-wide memory barrier (~1.5 us) each.
@@ -887,6 +887,12 @@ int pair_forward(rfk_mlp* const* trials, int w, int total_trials, const uint8_t*
     P.trial_stride = (long long)n * C;
     P.divisor = 1.0;
     P.div_mode = 0;
+    if (g_hook_set) {          // several trials per GPU in the peer step: carried sum only, the mean is the caller's
+      P.hook = g_hook;
+      g_hook_set = false;
+      RFK_REQUIRE(P.hook.n_owner == 0 && P.hook.n_wait == 0 && P.hook.n_signal == 0 && P.hook.skip_mean == 1,
+                  "pair kernel: a hook for several trials may only carry the previous step's sum");
+    }
   }
   {
     const char* dbg = getenv("RFK_PAIR_DEBUG");
@@ -991,7 +997,7 @@ int pair_forward(rfk_mlp* const* trials, int w, int total_trials, const uint8_t*
       fclose(f);
     }
   }
-  if (w > 1) {
+  if (w > 1 && !P.hook.skip_mean) {
     const float* ptrs[RFK_MAX_TRIALS];
     for (int t = 0; t < w; ++t) ptrs[t] = static_cast<const float*>(ws) + (size_t)t * (size_t)n * C;
     // float64 sum in trial order, divided by the size of the WHOLE ensemble, one rounding

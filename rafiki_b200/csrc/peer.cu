@@ -124,6 +124,58 @@ __global__ void peer_signal_kernel(const FlagPtrs flags, int count, unsigned int
   if (threadIdx.x < count) st_release_sys(flags.p[threadIdx.x], step);
 }
 
+// Scatter form with SEVERAL trials on this GPU: the trial kernel left per-trial probabilities in the scratch;
+// this kernel is kernel 3 and the hand-shake in one -- the rank's partial mean (float64 sum in trial order,
+// one division by the size of the whole ensemble, one rounding: ensemble.cu's arithmetic) goes straight into
+// the slot of the OWNER of each row with 16-byte stores, after the owners have released the slots
+// (`consumed`), and the last block raises `arrived[rank]` on every owner.
+struct ScatterMeanArgs {
+  const float* trial[RFK_MAX_TRIALS];
+  float* owner_out[kMaxRanks];            // this rank's slot in owner j's memory, indexed by global row
+  long long owner_vlo[kMaxRanks + 1];     // float4 index where owner j's rows begin
+  const unsigned int* wait_flags;
+  unsigned int* signal_flags[kMaxRanks];
+  unsigned int* counter;
+  long long n_vec;
+  double divisor;
+  unsigned int wait_value, signal_value;
+  int w, world;
+};
+__global__ void __launch_bounds__(kThreads) peer_scatter_mean_kernel(const __grid_constant__ ScatterMeanArgs a) {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");     // the next trial kernel may start its prologue
+  asm volatile("griddepcontrol.wait;" ::: "memory");                  // launched as a programmatic dependent of the trial kernel
+  if (threadIdx.x < a.world) {
+    if (!spin_until_ge(a.wait_flags + threadIdx.x, a.wait_value)) {
+      printf("rafiki_b200: scatter-mean timed out waiting for owner %d to release its slot\n", (int)threadIdx.x);
+      __trap();
+    }
+  }
+  __syncthreads();
+  const long long stride = (long long)gridDim.x * kThreads;
+  int j = 0;
+  for (long long i = (long long)blockIdx.x * kThreads + threadIdx.x; i < a.n_vec; i += stride) {
+    while (i >= a.owner_vlo[j + 1]) ++j;
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+    for (int t = 0; t < a.w; ++t) {
+      const float4 v = *reinterpret_cast<const float4*>(a.trial[t] + 4 * i);
+      s0 += (double)v.x; s1 += (double)v.y; s2 += (double)v.z; s3 += (double)v.w;
+    }
+    float4 o;
+    o.x = (float)(s0 / a.divisor); o.y = (float)(s1 / a.divisor);
+    o.z = (float)(s2 / a.divisor); o.w = (float)(s3 / a.divisor);
+    *reinterpret_cast<float4*>(a.owner_out[j] + 4 * i) = o;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    if (atomicAdd(a.counter, 1u) == gridDim.x - 1) {
+      atomicExch(a.counter, 0u);
+      __threadfence();
+      for (int q = 0; q < a.world; ++q) st_relaxed_sys(a.signal_flags[q], a.signal_value);
+    }
+  }
+}
+
 __global__ void peer_wait_kernel(const unsigned int* done_flags, int world, unsigned int step) {
   // it reads nothing but the flags: a kernel queued behind it as a programmatic dependent may start at once
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
@@ -257,7 +309,7 @@ namespace {
 
 struct PeerLayout {
   size_t buf_bytes, x_bytes, off_partial[2], off_result[2], off_x[2], off_slots[3], off_flags, total;
-  int f_arrived, f_consumed, f_counter, f_sumcounter, f_done;    // indices into the flag words (see below)
+  int f_arrived, f_consumed, f_counter, f_sumcounter, f_done, f_meancounter;    // indices into the flag words (see below)
 };
 
 PeerLayout peer_layout(int world, int64_t max_n, int d, int n_classes) {
@@ -279,6 +331,7 @@ PeerLayout peer_layout(int world, int64_t max_n, int d, int n_classes) {
   L.f_arrived = 3 * world + 1;
   L.f_consumed = 4 * world + 1;       // G words: owner j has consumed the slots it holds
   L.f_counter = 6 * world + 3;         // three words: the trial kernels of consecutive steps may overlap (step % 3)
+  L.f_meancounter = 6 * world + 6;     // block counter of the scatter-mean kernel
   L.f_sumcounter = 5 * world + 2;
   L.f_done = 5 * world + 3;           // G words (root): rank j's rows of the result are in place
   off += ((size_t)(6 * world + 8) * sizeof(unsigned int) + 255) / 256 * 256;
@@ -491,7 +544,7 @@ inline void owner_bounds(int64_t n, int G, int* bound) {
 
 // Scatter form, trial kernel of step `step`: every tile's partial means go to the owner of its rows.  With
 // carry_step != 0 the kernel also carries the reduction of that earlier step (batch carry_n) in its idle warp.
-int scatter_launch(rfk_peer* p, rfk_mlp_t* const* trials, int total_trials, const uint8_t* x, int64_t n, void* workspace,
+int scatter_launch(rfk_peer* p, rfk_mlp_t* const* trials, int w, int total_trials, const uint8_t* x, int64_t n, void* workspace,
                    size_t workspace_bytes, unsigned int step, unsigned int carry_step, int64_t carry_n, bool overlap,
                    void* stream) {
   const int G = p->world, k = (int)(step % 3);
@@ -539,15 +592,72 @@ int scatter_launch(rfk_peer* p, rfk_mlp_t* const* trials, int total_trials, cons
   }
   // overlap with the previous step's kernel only when both fill the chip (then a kernel three steps back, whose
   // block counter this one reuses, has certainly left: every CTA of a step replaces a CTA of the step before)
-  hook.no_grid_wait = overlap && (n + 255) / 256 >= rfk::num_sms() / 2 ? 1 : 0;
-  rfk::set_peer_hook(&hook);
-  const int rc = rfk_ensemble_forward(trials, 1, total_trials, x, n, hook.out_owner[p->rank], workspace, workspace_bytes, stream);
-  if (rfk::peer_hook_pending()) {      // the call did not reach the pair kernel after all
+  hook.no_grid_wait = overlap && w == 1 && (n + 255) / 256 >= rfk::num_sms() / 2 ? 1 : 0;
+  if (w == 1) {
+    rfk::set_peer_hook(&hook);
+    const int rc = rfk_ensemble_forward(trials, 1, total_trials, x, n, hook.out_owner[p->rank], workspace, workspace_bytes, stream);
+    if (rfk::peer_hook_pending()) {      // the call did not reach the pair kernel after all
+      rfk::set_peer_hook(nullptr);
+      rfk::set_error("peer_ensemble_step: internal routing error (hook not consumed)");
+      return RFK_ERR_INVALID;
+    }
+    return rc;
+  }
+  // ---- several trials on this GPU: the trial kernel carries the previous step's sum and leaves per-trial
+  // probabilities in the scratch; the scatter-mean kernel is kernel 3 and the hand-shake in one
+  const size_t need = rfk::pair_workspace_bytes(w, p->n_classes, n);
+  RFK_REQUIRE(workspace != nullptr && workspace_bytes >= need,
+              "peer_ensemble_step: %zu bytes of workspace needed for %d trials per GPU (every rank must pass it: the "
+              "ranks choose the form of the step together)", need, w);
+  ScatterMeanArgs a;
+  memset(&a, 0, sizeof(a));
+  for (int t = 0; t < w; ++t)
+    a.trial[t] = static_cast<const float*>(workspace) + (size_t)t * (size_t)n * (size_t)p->n_classes;
+  for (int j = 0; j < G; ++j) {
+    a.owner_out[j] = hook.out_owner[j];
+    a.signal_flags[j] = hook.signal_flags[j];
+    a.owner_vlo[j] = (long long)hook.owner_bound[j] * 256 * p->n_classes / 4;
+  }
+  a.n_vec = n * (long long)p->n_classes / 4;
+  a.owner_vlo[G] = a.n_vec;
+  for (int j = 0; j < G; ++j)
+    if (a.owner_vlo[j] > a.n_vec) a.owner_vlo[j] = a.n_vec;
+  a.wait_flags = hook.wait_flags;
+  a.wait_value = hook.wait_value;
+  a.signal_value = hook.signal_value;
+  a.counter = my_flags + p->L.f_meancounter;
+  a.divisor = (double)total_trials;
+  a.w = w;
+  a.world = G;
+  rfk::PeerHook carry_only = hook;
+  carry_only.n_wait = carry_only.n_signal = carry_only.n_owner = 0;
+  carry_only.no_grid_wait = 0;
+  carry_only.skip_mean = 1;
+  rfk::set_peer_hook(&carry_only);
+  const int rc = rfk_ensemble_forward(trials, w, total_trials, x, n, hook.out_owner[p->rank], workspace, workspace_bytes, stream);
+  if (rfk::peer_hook_pending()) {
     rfk::set_peer_hook(nullptr);
     rfk::set_error("peer_ensemble_step: internal routing error (hook not consumed)");
     return RFK_ERR_INVALID;
   }
-  return rc;
+  if (rc != RFK_OK) return rc;
+  const long long want = (a.n_vec + kThreads - 1) / kThreads;
+  const int grid = (int)(want < 1 ? 1 : (want < (long long)rfk::num_sms() * 4 ? want : (long long)rfk::num_sms() * 4));
+  {
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(kThreads);
+    cfg.stream = reinterpret_cast<cudaStream_t>(stream);
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = getenv("RFK_NO_PDL") == nullptr ? 1 : 0;
+    RFK_CUDA_TRY(cudaLaunchKernelEx(&cfg, peer_scatter_mean_kernel, a));
+  }
+  RFK_LAUNCH_CHECK("peer_scatter_mean_kernel");
+  return RFK_OK;
 }
 
 // Scatter form, stand-alone reduction of step `step`: my rows of the G slots -> the root's result; the root then
@@ -580,9 +690,17 @@ int scatter_sum(rfk_peer* p, unsigned int step, int64_t n, void* stream) {
   return RFK_OK;
 }
 
+// Every rank must reach the same answer: with trials dealt t % world a rank holds at least one trial exactly
+// when total_trials >= world, and the other conditions do not depend on the rank.
 bool scatter_capable(const rfk_peer* p, rfk_mlp_t* const* trials, int w, int total_trials, int64_t n) {
-  return w == 1 && total_trials == p->world && p->world > 1 && trials != nullptr && trials[0]->fusable &&
-         trials[0]->dtype != RFK_F32 && rfk::pair_applicable(trials[0]->d, n);
+  if (w < 1 || total_trials < p->world || p->world <= 1 || trials == nullptr) return false;
+  static const bool multi = getenv("RFK_PEER_NO_MULTI_SCATTER") == nullptr;
+  if (total_trials != p->world && !multi) return false;      // (a rank-independent condition)
+  for (int t = 0; t < w; ++t)
+    if (trials[t] == nullptr || !trials[t]->fusable || trials[t]->dtype == RFK_F32 || trials[t]->dtype != trials[0]->dtype ||
+        trials[t]->d != trials[0]->d)
+      return false;
+  return rfk::pair_applicable(trials[0]->d, n);
 }
 
 }  // namespace
@@ -622,7 +740,7 @@ extern "C" int rfk_peer_ensemble_step(rfk_peer_t* p, rfk_mlp_t* const* trials, i
     const bool scatter = scatter_capable(p, trials, w, total_trials, n);
     const unsigned int wait_value = step >= 2 ? step - 2 : 0;
     if (scatter) {
-      int rc = scatter_launch(p, trials, total_trials, x, n, workspace, workspace_bytes, step, 0, 0, false, stream);
+      int rc = scatter_launch(p, trials, w, total_trials, x, n, workspace, workspace_bytes, step, 0, 0, false, stream);
       if (rc != RFK_OK) return rc;
       rc = scatter_sum(p, step, n, stream);
       if (rc != RFK_OK) return rc;
@@ -730,7 +848,7 @@ extern "C" int rfk_peer_ensemble_step_pipelined(rfk_peer_t* p, rfk_mlp_t* const*
   p->held_result = nullptr;
   const unsigned int step = ++p->rstep;
   const unsigned int carry = p->pending_step;
-  const int rc = scatter_launch(p, trials, total_trials, x, n, workspace, workspace_bytes, step, carry, p->pending_n,
+  const int rc = scatter_launch(p, trials, w, total_trials, x, n, workspace, workspace_bytes, step, carry, p->pending_n,
                                 p->inputs_resident, stream);
   if (rc != RFK_OK) return rc;
   if (carry != 0) {

@@ -77,6 +77,10 @@ struct PeerHook {
   // programmatic dependent, then does not wait for the previous grid at all (its first CTAs run while the last
   // CTAs of the previous step finish and publish their flags).
   int no_grid_wait;
+  // Several trials on this GPU: the trial kernel writes per-trial probabilities to the scratch and carries the
+  // previous step's sum only (no owners, no flags of its own); the caller runs the scatter-mean kernel next,
+  // so the library's own kernel 3 is skipped.
+  int skip_mean;
 };
 void set_peer_hook(const PeerHook* hook);     // thread-local; consumed (and cleared) by the next pair_forward with w == 1
 bool peer_hook_pending();
