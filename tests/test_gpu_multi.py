@@ -22,7 +22,7 @@ def _free_port():
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason='needs at least 2 GPUs')
-@pytest.mark.parametrize('n_trials', [5, 2])      # 3 + 2 trials per rank; one trial per rank (hand-shake inside the kernel)
+@pytest.mark.parametrize('n_trials', [5, 2, 3])   # 3 + 2 trials per rank (scatter-mean kernel); one per rank (hand-shake inside the trial kernel); 2 + 1 (both)
 def test_peer_ensemble_equals_the_single_gpu_ensemble(n_trials):
     world = 2
     cmd = [sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node', str(world),
