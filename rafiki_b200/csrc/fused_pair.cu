@@ -480,36 +480,38 @@ fused_pair_kernel(const __grid_constant__ PairParams P, const __grid_constant__ 
       if (!(dbg & 8)) mbar_wait(&bars->raw_full[rstage], rphase);
       PROF(1);
       if (warp == kEpiWarps) PTRACE(0, 1);
+      // The two atoms are handed over one at a time: the first goes to the issuer as soon as ITS stage was free
+      // and its 64 bytes are in tensor memory, while the second may still be waiting for a stage to come back
+      // (stages return one MMA group, ~256 cycles, apart).
       if (round0 > 0) mbar_wait(&bars->a_free[as0], (uint32_t)((round0 - 1) & 1));
-      if (two && round1 > 0) mbar_wait(&bars->a_free[as1], (uint32_t)((round1 - 1) & 1));
       PROF(3);
       if (warp == kEpiWarps) PTRACE(0, 2);
       tc_fence_after_sync();
       const uint32_t rsrc = raw_row + (uint32_t)rstage * RAW_STAGE;
       const uint32_t dst0 = a_dst0 + (uint32_t)as0 * A_COLS, dst1 = a_dst0 + (uint32_t)as1 * A_COLS;
       const int left = P.d - atom0 * ATOM_K;                // K elements of this row from here on (> 0)
-      if (left >= 2 * ATOM_K) {                             // the common case: both atoms whole
-        convert32(rsrc, 0u, dst0);
-        convert32(rsrc, 2u, dst0 + 16u);
-        convert32(rsrc, 4u, dst1);
-        convert32(rsrc, 6u, dst1 + 16u);
-      } else {                                              // the last raw stage of a row: only the 16-byte chunks the MMAs read
-        const int live = (left + 15) >> 4;                  // 1 .. 7 chunks
-        convert32(rsrc, 0u, dst0);
-        if (live > 2) convert32(rsrc, 2u, dst0 + 16u);
+      const int live = left >= 2 * ATOM_K ? 8 : (left + 15) >> 4;     // 16-byte chunks the MMAs read: 1 .. 8
+      convert32(rsrc, 0u, dst0);
+      if (live > 2) convert32(rsrc, 2u, dst0 + 16u);
+      tmem_st_wait();
+      tc_fence_before_sync();
+      __syncwarp();
+      if (lane0) mbar_arrive_cluster(l_a_full0 + 8u * as0);
+      PROF(2);
+      if (two) {
+        if (round1 > 0) mbar_wait(&bars->a_free[as1], (uint32_t)((round1 - 1) & 1));
+        tc_fence_after_sync();
         if (live > 4) convert32(rsrc, 4u, dst1);
         if (live > 6) convert32(rsrc, 6u, dst1 + 16u);
       }
-      PROF(2);
       __syncwarp();
       if (lane0 && !(dbg & 8)) mbar_arrive(&bars->raw_empty[rstage]);      // the bytes are in registers
-      tmem_st_wait();
-      PROF(4);
-      tc_fence_before_sync();
-      __syncwarp();
-      if (lane0) {
-        mbar_arrive_cluster(l_a_full0 + 8u * as0);
-        if (two) mbar_arrive_cluster(l_a_full0 + 8u * as1);
+      if (two) {
+        tmem_st_wait();
+        PROF(4);
+        tc_fence_before_sync();
+        __syncwarp();
+        if (lane0) mbar_arrive_cluster(l_a_full0 + 8u * as1);
       }
       PROF(5);
       if (warp == kEpiWarps) PTRACE(0, 3);

@@ -3,6 +3,3 @@
 O=gpurun_out/${1:-dbg}; mkdir -p $O; rm -f $O/*
 timeout 300 python tools/pair_check.py > $O/pair_check.log 2>&1; echo "pair_check rc=$?"; grep -v "timed out" $O/pair_check.log | tail -2
 RFK_ITERS=50 timeout 120 python tools/time_fused.py 8x65536 4x65536 2x65536 1x65536 1x20000 2>&1 | grep -v "timed out" | tee $O/time.log
-RFK_NO_PDL=1 RFK_ITERS=50 timeout 120 python tools/time_fused.py 8x65536 1x65536 2>&1 | grep -v "timed out" | sed 's/^/nopdl /' | tee -a $O/time.log
-timeout 900 python -m pytest tests -q -m gpu -x 2>&1 | tail -2
-timeout 300 python tools/stress_determinism.py --reps 25 --hetero --load 2>&1 | grep STRESS
