@@ -31,6 +31,20 @@ def test_every_declared_symbol_is_exported_and_bound():
     assert sorted(_native.PROTOTYPES) == declared
 
 
+def test_prototypes_take_as_many_arguments_as_the_header_declares():
+    text = open(os.path.join(ROOT, 'include', 'rafiki_b200.h')).read()
+    text = re.sub(r'/\*.*?\*/', '', text, flags=re.S)
+    text = re.sub(r'//[^\n]*', '', text)
+    seen = 0
+    for name, args in re.findall(r'\b(rfk_[a-z0-9_]+)\s*\(([^;{]*?)\)\s*;', text, flags=re.S):
+        args = args.strip()
+        n_args = 0 if args in ('', 'void') else args.count(',') + 1
+        assert len(_native.PROTOTYPES[name][1]) == n_args, '%s: header declares %d arguments, ctypes prototype %d' % (
+            name, n_args, len(_native.PROTOTYPES[name][1]))
+        seen += 1
+    assert seen == len(_native.PROTOTYPES)
+
+
 def test_version_and_error_channel():
     lib = _native.load()
     assert lib.rfk_version() == 100
