@@ -184,7 +184,7 @@ def test_resize_folds_into_the_first_layer():
     from oracle import feedforward as ff
     from rafiki_b200 import synth
     from rafiki_b200.engine import fold_resize_into_params
-    for S, s_in, ch in ((32, 28, 1), (48, 28, 1), (32, 28, 3)):
+    for S, s_in, ch in ((32, 28, 1), (48, 28, 1), (32, 28, 3), (28, 40, 1), (32, 32, 1)):     # enlarge, reduce, same size
         p = synth.make_trial(3, S, ch, 2, 36, data_kind='fashion')
         q = synth.make_queries(40, s_in, ch, 'fashion', seed=2)
         want = ff.forward(p, ff.resize_as_images(q.tolist(), [S, S]), np.float64)
