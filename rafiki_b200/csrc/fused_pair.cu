@@ -15,13 +15,17 @@
 // kernel 3 (ensemble.cu) over those, in float64 in trial order with one rounding -- the same sum
 // the single-CTA kernel keeps in registers.
 //
-// Roles per CTA (640 threads, as in fused_trial.cu): epilogue x 8 warps, converters x 8 (uint8 ->
-// fp16 into tensor memory; a warp converts its rows of a whole raw stage, two groups alternate stages), loader (TMA of raw tiles; bulk copies of the weights at a trial
-// change), layer-1 MMA issuer and layers-2/3 MMA issuer (LEADER CTA only: one thread issues for
-// both CTAs), and a warp that forwards "weights landed" to the leader.  Hand-offs that cross the
-// pair (operands ready, accumulator drained) are arrivals on the leader's mbarriers through the
-// cluster window; completions come back as tcgen05.commit multicast to both CTAs.  No load here is
-// a multicast load: every CTA fetches its own bytes.
+// Roles per CTA (640 threads, as in fused_trial.cu): epilogue x 8 warps (hidden layers; the half-0
+// warps also turn logits into staged probabilities, the half-1 warps store the staged tile), converters
+// x 8 (uint8 -> fp16 into tensor memory; a warp converts its rows of a whole raw stage and hands its
+// two K atoms over one at a time, two groups of four warps alternate stages), loader (TMA of raw
+// tiles; bulk copies of the weights at a trial change), layer-1 MMA issuer and layers-2/3 MMA issuer
+// (LEADER CTA only: one thread issues for both CTAs), and a warp that forwards "weights landed" to the
+// leader and, in the multi-GPU step, carries the previous batch's cross-rank sum.  Hand-offs that
+// cross the pair (operands ready, accumulator drained) are arrivals on the leader's mbarriers through
+// the cluster window; completions come back as tcgen05.commit multicast to both CTAs.  No load here
+// is a multicast load: every CTA fetches its own bytes.  The kernel is launched as a programmatic
+// dependent of the previous kernel of its stream (griddep_wait below).
 #include <stdlib.h>
 
 #include <atomic>
