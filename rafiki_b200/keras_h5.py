@@ -24,7 +24,6 @@ tf.keras 1.12 produces: ``keras/engine/saving.py``), not against a file TensorFl
 """
 import base64
 import json
-import struct
 
 import numpy as np
 
